@@ -1,0 +1,225 @@
+/* rrt.h — C ABI of librrt.so: the B200 (sm_100a) path-tracing hot path of RustRayTrace.
+ *
+ * This is the drop-in boundary.  It generalises the only C-shaped seam
+ * the reference has —
+ *     fn render(camera: CameraUniform, spheres: &[SphereGpu], materials: &[MaterialGpu])
+ *         -> Result<(), String>                       (src/cuda/mod.rs:342, src/gpu/mod.rs:308)
+ *     write_ppm_from_accum(width, height, accum: &[f32], spp)      (src/render_io.rs:3)
+ * — from "spheres + 3 materials" to the whole scene graph of the three books.
+ *
+ * The host (Rust in the reference; the C++ mirror in rustraytrace_b200/host here) walks its
+ * HittableObject tree once and emits the arrays below (one rrt_hittable per Arc<HittableObject>,
+ * in construction order).  The library deep-copies, bakes instances, builds its own BVH,
+ * uploads SoA buffers and renders.  All host pointers are borrowed for the duration of the call
+ * only (as htod_sync_copy borrows its slices, src/cuda/mod.rs:389-390).
+ *
+ * Errors: 0 = ok, negative rrt_status otherwise, text via rrt_last_error() (thread-local),
+ * replacing Result<(), String> (src/cuda/mod.rs:342-441).  Never aborts; never falls back to CPU.
+ * Threading: blocking calls from one host thread per context; one context = one CUDA device.
+ */
+#ifndef RRT_H
+#define RRT_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum rrt_status {
+  RRT_OK = 0,
+  RRT_ERR_INVALID = -1,     /* bad argument / malformed scene description */
+  RRT_ERR_CUDA = -2,        /* CUDA runtime error ("cuda init failed", "kernel launch failed" …) */
+  RRT_ERR_UNSUPPORTED = -3, /* scene uses a construct the flattener does not cover */
+  RRT_ERR_NO_DEVICE = -4    /* no CUDA device: there is no CPU fallback */
+} rrt_status;
+
+/* ---- scene description (host side, f64 like every reference CPU quantity) ---------------- */
+
+/* HittableObject variants, the_rest_of_your_life/hittable.rs:180-188 */
+typedef enum rrt_hittable_kind {
+  RRT_H_SPHERE = 0,          /* sphere.rs:11-45   a=center0, b=center1-center0, c[0]=radius       */
+  RRT_H_QUAD = 1,            /* quad.rs:11-48     a=Q, b=u, c=v                                   */
+  RRT_H_LIST = 2,            /* hittable_list.rs  children[first_child .. +n_children)           */
+  RRT_H_BVH = 3,             /* bvh.rs:16-19      BvhNode::new(list): children = the list        */
+  RRT_H_TRANSLATE = 4,       /* hittable.rs:73-84 child=first_child, a=offset                     */
+  RRT_H_ROTATE_Y = 5,        /* hittable.rs:100-140 child=first_child, a[0]=angle in degrees      */
+  RRT_H_CONSTANT_MEDIUM = 6  /* constant_medium.rs:10-37 boundary=first_child, a[0]=density,
+                                material = the Isotropic phase function                          */
+} rrt_hittable_kind;
+
+typedef struct rrt_hittable {
+  int32_t kind;
+  int32_t material;    /* index into materials[]; -1 for containers */
+  int32_t first_child; /* LIST/BVH: offset into children[]; TRANSLATE/ROTATE_Y/MEDIUM: hittable index */
+  int32_t n_children;  /* LIST/BVH only */
+  double a[3];
+  double b[3];
+  double c[3];
+} rrt_hittable;
+
+/* MaterialObject variants, the_rest_of_your_life/material.rs:195-202 */
+typedef enum rrt_material_kind {
+  RRT_M_LAMBERTIAN = 0,   /* texture */
+  RRT_M_METAL = 1,        /* albedo, fuzz (already min(fuzz,1), material.rs:79-81) */
+  RRT_M_DIELECTRIC = 2,   /* refraction_index */
+  RRT_M_DIFFUSE_LIGHT = 3,/* texture */
+  RRT_M_ISOTROPIC = 4,    /* texture */
+  RRT_M_EMPTY = 5         /* EmptyMaterial (light proxies), material.rs:192-193 */
+} rrt_material_kind;
+
+typedef struct rrt_material {
+  int32_t kind;
+  int32_t texture; /* index into textures[] or -1 */
+  double albedo[3];
+  double fuzz;
+  double refraction_index;
+} rrt_material;
+
+/* TextureObject variants, the_rest_of_your_life/texture.rs:128-133 */
+typedef enum rrt_texture_kind {
+  RRT_T_SOLID = 0,   /* color */
+  RRT_T_CHECKER = 1, /* scale (inv_scale = 1/scale, texture.rs:51), even, odd = texture indices */
+  RRT_T_IMAGE = 2,   /* image = index into images[]; missing image => height 0 => cyan (texture.rs:91-93) */
+  RRT_T_NOISE = 3    /* scale, perlin = index into perlins[] */
+} rrt_texture_kind;
+
+typedef struct rrt_texture {
+  int32_t kind;
+  int32_t even;   /* checker */
+  int32_t odd;    /* checker */
+  int32_t image;  /* image  */
+  int32_t perlin; /* noise  */
+  int32_t _pad;
+  double color[3];
+  double scale;
+} rrt_texture;
+
+/* RtwImage after image::open(..).to_rgb8(), rtw_image.rs:57-67: row-major RGB8 */
+typedef struct rrt_image {
+  int32_t width, height;
+  const uint8_t* rgb; /* width*height*3 bytes, NULL/0x0 when the file was not found */
+} rrt_image;
+
+/* Perlin tables, perlin.rs:4-23 */
+typedef struct rrt_perlin {
+  double randvec[256][3];
+  int32_t perm_x[256], perm_y[256], perm_z[256];
+} rrt_perlin;
+
+typedef struct rrt_scene_desc {
+  const rrt_hittable* hittables; int32_t n_hittables;
+  const int32_t* children;       int32_t n_children;   /* hittable indices, for LIST/BVH */
+  const rrt_material* materials; int32_t n_materials;
+  const rrt_texture* textures;   int32_t n_textures;
+  const rrt_image* images;       int32_t n_images;
+  const rrt_perlin* perlins;     int32_t n_perlins;
+  int32_t world;  /* hittable index of the object passed to Camera::render as `world` */
+  int32_t lights; /* hittable index of book 3's `lights` list (camera.rs:63), or -1 */
+} rrt_scene_desc;
+
+/* Camera pub fields, the_rest_of_your_life/camera.rs:15-29 (book 1 lacks `background`). */
+typedef struct rrt_camera {
+  double aspect_ratio;
+  int32_t image_width;
+  int32_t samples_per_pixel;
+  int32_t max_depth;
+  int32_t _pad;
+  double background[3];
+  double vfov;
+  double lookfrom[3];
+  double lookat[3];
+  double vup[3];
+  double defocus_angle;
+  double focus_dist;
+} rrt_camera;
+
+/* Which book's Camera::ray_color / get_ray to run. */
+typedef enum rrt_integrator {
+  RRT_INT_BOOK1 = 1, /* in_one_weekend/camera.rs:152-209: sky gradient, no emission, no ray time */
+  RRT_INT_BOOK2 = 2, /* the_next_week/camera.rs:148-201: background colour, emitted, ray time   */
+  RRT_INT_BOOK3 = 3  /* the_rest_of_your_life/camera.rs:156-254: stratified, mixture-PDF lights */
+} rrt_integrator;
+
+/* How one rank's share of the frame is chosen.  Every (pixel, sample) draws its
+ * randomness from Philox keyed on (seed; pixel, sample, bounce), so any partition gives the same
+ * per-sample radiance. */
+typedef enum rrt_shard_mode {
+  RRT_SHARD_NONE = 0,
+  RRT_SHARD_TILE = 1,  /* interleaved 32x32-pixel tiles: tile k belongs to rank k % world */
+  RRT_SHARD_SAMPLE = 2 /* samples [rank*n/world, (rank+1)*n/world) of every pixel          */
+} rrt_shard_mode;
+
+typedef struct rrt_render_params {
+  int32_t integrator; /* rrt_integrator */
+  int32_t shard_mode; /* rrt_shard_mode */
+  int32_t rank;
+  int32_t world;
+  uint64_t seed;
+} rrt_render_params;
+
+/* Filled by every render call. */
+typedef struct rrt_stats {
+  int32_t width, height;
+  int32_t spp_effective;   /* spp, or floor(sqrt(spp))^2 for book 3 (camera.rs:114-116) */
+  int32_t kernel_launches; /* CUDA kernels of this library launched by the last call */
+  double paths;            /* camera paths traced by this rank in the last call */
+  double kernel_ms;        /* device time of the path-tracing kernel (CUDA events, its own stream) */
+  double total_ms;         /* device time of the whole call's stream work */
+  uint64_t h2d_bytes, d2h_bytes;
+  int32_t n_prims, n_bvh_nodes, n_media, n_lights;
+  int32_t sm_count;
+  int32_t _pad;
+} rrt_stats;
+
+typedef struct rrt_ctx rrt_ctx;
+typedef struct rrt_scene rrt_scene;
+
+/* CudaDevice::new(0), src/cuda/mod.rs:343.  One context per process-and-GPU. */
+int rrt_init(int device, rrt_ctx** out);
+void rrt_shutdown(rrt_ctx* ctx);
+
+/* htod of the scene, src/cuda/mod.rs:389-390 — plus instance baking and the BVH build that
+ * replace BvhNode::new (bvh.rs:21-156). */
+int rrt_scene_create(rrt_ctx* ctx, const rrt_scene_desc* desc, rrt_scene** out);
+void rrt_scene_destroy(rrt_scene* scene);
+
+/* Image height as Camera::initialize computes it (camera.rs:109-112). */
+int rrt_image_height(const rrt_camera* cam);
+
+/* The render loop of src/cuda/mod.rs:403-436 / Camera::render (camera.rs:63-106): traces this
+ * rank's share and writes row-major RGBA f32 sums, .w = samples accumulated
+ * (layout of src/render_io.rs:11, src/cuda/mod.rs:330-332).
+ *   rrt_render:        accum_host is caller-allocated W*H*4 floats; includes the D2H copy.
+ *   rrt_render_device: accum_dev is a device pointer (W*H*4 floats) on this context's GPU; the call
+ *                      returns after the kernels completed; nothing leaves HBM. */
+int rrt_render(rrt_ctx* ctx, const rrt_scene* scene, const rrt_camera* cam,
+               const rrt_render_params* params, float* accum_host);
+int rrt_render_device(rrt_ctx* ctx, const rrt_scene* scene, const rrt_camera* cam,
+                      const rrt_render_params* params, float* accum_dev);
+
+/* One-shot twin of cuda::imp::render (src/cuda/mod.rs:342-441): upload, render, read back, free. */
+int rrt_render_frame(rrt_ctx* ctx, const rrt_scene_desc* desc, const rrt_camera* cam,
+                     const rrt_render_params* params, float* accum_host);
+
+/* Deterministic probe: one pixel-centre ray per pixel from the camera centre (no jitter, no
+ * defocus, time 0), constant media excluded.  prim_id = index into desc->hittables of the closest
+ * leaf (or -1), t = ray parameter in units of |direction| (ray.rs:31-33).  Host outputs, W*H each.
+ * precision: 64 = f64 kernel (parity gate), 32 = the f32 intersection code of the render kernel. */
+int rrt_probe(rrt_ctx* ctx, const rrt_scene* scene, const rrt_camera* cam, int precision,
+              int32_t* prim_id, double* t);
+
+/* write_ppm_from_accum's per-pixel arithmetic (src/render_io.rs:8-26) on the device:
+ * accum (device, RGBA f32) -> rgb8 (device, W*H*3).  spp<=0 uses accum.w per pixel. */
+int rrt_resolve_rgb8_device(rrt_ctx* ctx, const float* accum_dev, int width, int height, int spp,
+                            uint8_t* rgb_dev);
+/* Same, host in / host out (copies inside). */
+int rrt_resolve_rgb8(rrt_ctx* ctx, const float* accum_host, int width, int height, int spp,
+                     uint8_t* rgb_host);
+
+int rrt_get_stats(const rrt_ctx* ctx, rrt_stats* out);
+const char* rrt_last_error(void);
+const char* rrt_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RRT_H */

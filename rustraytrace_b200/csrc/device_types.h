@@ -1,0 +1,142 @@
+// device_types.h — HBM layout of a flattened scene (shared by the host flattener and the kernels).
+//
+// Everything the reference keeps as an Arc<enum> pointer tree (hittable.rs:180-188) is baked into
+// flat arrays:
+//   prims   : one 64-byte record (4 x float4) per world-space leaf primitive, stored in BVH-leaf
+//             order so a leaf is a contiguous run; within a leaf spheres come first, then quads.
+//   nodes   : one 64-byte record per inner BVH node holding BOTH children's boxes, breadth-first,
+//             so the top of the tree can be staged in shared memory as a prefix.
+//   bprims  : boundary primitives of constant media (same record format), outside the BVH.
+//   prims64 : f64 twin of prims (16 doubles per record) for the probe kernel.
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#include <cuda_runtime.h>
+#else
+struct float4 { float x, y, z, w; };
+#endif
+
+namespace rrt {
+
+// ---- prim record (float4 p[4]) -------------------------------------------------------------
+// sphere: p0 = (c0.x, c0.y, c0.z, r)       p1 = (dc.x, dc.y, dc.z, 1/r)
+//         p2 = (mat, id, order, flags) as int bits   p3 = (uv_cos, uv_sin, 0, 0)
+// quad:   p0 = (n.x, n.y, n.z, d)           p1 = (A.x, A.y, A.z, a0)   alpha = p.A + a0
+//         p2 = (B.x, B.y, B.z, b0)          p3 = (mat, id, order, flags) as int bits
+//   with A = v x w, B = w x u, a0 = -Q.A, b0 = -Q.B  (quad.rs:76-79: alpha = w.(hp x v) = hp.(v x w))
+// f64 twin (double q[16]):
+// sphere: q0..2 = c0, q3 = r, q4..6 = dc
+// quad:   q0..2 = n, q3 = d, q4..6 = Q, q7..9 = u, q10..12 = v, q13..15 = w   (quad.rs formulas verbatim)
+enum PrimKind { PRIM_SPHERE = 0, PRIM_QUAD = 1 };
+enum PrimFlags { PF_UV_ROTATED = 1 };
+
+// ---- BVH inner node (float4 n[4]) ------------------------------------------------------------
+// n0 = (c0.lo.x, c0.hi.x, c0.lo.y, c0.hi.y)   n1 = (c1.lo.x, c1.hi.x, c1.lo.y, c1.hi.y)
+// n2 = (c0.lo.z, c0.hi.z, c1.lo.z, c1.hi.z)   n3 = (ref0, ref1, 0, 0) as int bits
+// ref >= 0: inner node index.  ref < 0: leaf, ~ref = (first << 8) | (n_spheres << 4) | n_quads.
+static const int LEAF_MAX_PER_KIND = 15;
+inline
+#if defined(__CUDACC__)
+__host__ __device__
+#endif
+int make_leaf_ref(int first, int nsph, int nquad) { return ~((first << 8) | (nsph << 4) | nquad); }
+
+struct DevMaterial {  // 32 B
+  int kind;           // rrt_material_kind
+  int tex;            // texture index or -1
+  float fuzz;
+  float ior;
+  float4 albedo;      // metal albedo; for textured kinds a copy of a solid colour (fast path flag in .w)
+};
+
+struct DevTexture {   // 32 B
+  int kind;           // rrt_texture_kind
+  int a;              // checker: even   image: image index   noise: perlin index
+  int b;              // checker: odd
+  int pad;
+  float4 v;           // solid: rgb    checker: .w = inv_scale    noise: .w = scale
+};
+
+struct DevImage {
+  int width, height;
+  int offset;         // first texel in the uchar4 texel pool
+  int pad;
+};
+
+// Perlin tables (perlin.rs:4-9): 256 gradient vectors + three permutations
+struct DevPerlin {
+  float4 randvec[256];
+  uint8_t perm[3][256];
+};
+
+struct DevMedium {    // constant_medium.rs:10-14
+  int first, nsph, nquad;  // boundary run in bprims
+  int mat;                 // Isotropic phase function
+  float neg_inv_density;
+  int id;                  // desc index of the medium
+  int pad0, pad1;
+};
+
+// light list entry (lights of camera.rs:63; hittable_list.rs:60-75)
+// kind 0 sphere: a = (c, r)
+// kind 1 quad:   a = (n, d), b = (A, a0), c = (B, b0), q = (Q, area), u = (u, 0), v = (v, 0)
+// kind 2 other:  pdf_value 0, random (1,0,0)  (trait defaults, hittable.rs:58-64)
+struct DevLight {
+  float4 a, b, c, q, u, v;
+  int kind, pad0, pad1, pad2;
+};
+
+// CameraInternals (camera.rs:49-60), f32, direction kept relative to the centre
+struct DevCamera {
+  float cx, cy, cz;          // center
+  float p00x, p00y, p00z;    // pixel00_loc - center
+  float dux, duy, duz;       // pixel_delta_u
+  float dvx, dvy, dvz;       // pixel_delta_v
+  float ddux, dduy, dduz;    // defocus_disk_u
+  float ddvx, ddvy, ddvz;    // defocus_disk_v
+  float bgx, bgy, bgz;       // background
+  float recip_sqrt_spp;
+  int sqrt_spp;
+  int defocus;               // defocus_angle > 0
+};
+struct DevCamera64 {
+  double c[3], p00[3], du[3], dv[3];
+};
+
+struct DevScene {
+  const float4* prims;
+  const float4* nodes;
+  const float4* bprims;
+  const double* prims64;
+  const DevMaterial* materials;
+  const DevTexture* textures;
+  const DevImage* images;
+  const unsigned char* texels;  // uchar4 pool (r,g,b,255)
+  const DevPerlin* perlins;
+  const DevMedium* media;
+  const DevLight* lights;
+  int root_ref;
+  int n_nodes, n_prims, n_media, n_lights;
+  int has_motion;    // any sphere with dc != 0
+  int smem_nodes;    // how many leading nodes the kernel stages in shared memory
+  int smem_prims;    // how many leading prims are staged after them
+};
+
+// One launch's share of the frame.
+struct DevWork {
+  int width, height;
+  int tiles_x;          // 8x4-pixel warp tiles per row
+  int n_tiles;          // warp tiles owned by this rank
+  int chunks;           // sample chunks per tile
+  int s_begin, s_end;   // sample range of this rank
+  int shard_mode, rank, world;
+  int stiles_x, stiles_y;   // 32x32 super tiles (tile sharding)
+  int integrator;
+  int max_depth;
+  int spp_eff;
+  unsigned seed_lo, seed_hi;
+  int atomic_accum;     // chunks > 1: accumulate with red.add
+};
+
+}  // namespace rrt

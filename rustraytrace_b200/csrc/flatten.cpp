@@ -1,0 +1,558 @@
+// flatten.cpp — see flatten.hpp.  Host-only C++17, f64 throughout; f32 conversion happens at the
+// very end and is conservative for boxes.
+#include "flatten.hpp"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <queue>
+
+namespace rrt {
+namespace {
+
+struct D3 {
+  double x, y, z;
+  D3() : x(0), y(0), z(0) {}
+  D3(double a, double b, double c) : x(a), y(b), z(c) {}
+  explicit D3(const double* p) : x(p[0]), y(p[1]), z(p[2]) {}
+  double operator[](int i) const { return i == 0 ? x : (i == 1 ? y : z); }
+};
+inline D3 operator+(D3 a, D3 b) { return D3(a.x + b.x, a.y + b.y, a.z + b.z); }
+inline D3 operator-(D3 a, D3 b) { return D3(a.x - b.x, a.y - b.y, a.z - b.z); }
+inline D3 operator*(double s, D3 a) { return D3(s * a.x, s * a.y, s * a.z); }
+inline double dot(D3 a, D3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+inline D3 cross(D3 a, D3 b) { return D3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
+
+// object -> world: p_w = R p + t with R a rotation about Y (hittable.rs:158-170: x = c x' + s z',
+// z = -s x' + c z').
+struct Xform {
+  double c = 1.0, s = 0.0;
+  D3 t;
+  bool rotated = false;
+  D3 rot(D3 p) const { return D3(c * p.x + s * p.z, p.y, -s * p.x + c * p.z); }
+  D3 point(D3 p) const { return rot(p) + t; }
+};
+
+struct BakedPrim {
+  int kind = 0, id = -1, order = 0, mat = -1, flags = 0;
+  D3 c0, dc; double r = 0;            // sphere
+  D3 Q, u, v, n, w; double d = 0, area = 0;  // quad
+  double uvcos = 1, uvsin = 0;
+  double lo[3], hi[3];
+};
+
+void pad_axis(double& lo, double& hi) {  // Aabb::pad_to_minimums, aabb.rs:107-118
+  const double delta = 0.0001;
+  if (hi - lo < delta) { lo -= delta / 2; hi += delta / 2; }
+}
+
+void bake_sphere(const rrt_hittable& h, int id, const Xform& X, BakedPrim& p) {
+  p.kind = PRIM_SPHERE; p.id = id; p.mat = h.material;
+  p.c0 = X.point(D3(h.a));
+  p.dc = X.rot(D3(h.b));
+  p.r = std::max(h.c[0], 0.0);  // sphere.rs:23 radius.max(0.0)
+  p.uvcos = X.c; p.uvsin = X.s;
+  if (X.rotated) p.flags |= PF_UV_ROTATED;
+  double rr = std::fabs(h.c[0]);
+  D3 c1 = p.c0 + p.dc;
+  for (int a = 0; a < 3; ++a) {
+    p.lo[a] = std::min(p.c0[a], c1[a]) - rr;
+    p.hi[a] = std::max(p.c0[a], c1[a]) + rr;
+    pad_axis(p.lo[a], p.hi[a]);
+  }
+}
+
+void quad_derive(BakedPrim& p) {  // Quad::new, quad.rs:24-48
+  D3 n = cross(p.u, p.v);
+  double len = std::sqrt(dot(n, n));
+  p.n = D3(n.x / len, n.y / len, n.z / len);
+  p.d = dot(p.n, p.Q);
+  double nn = dot(n, n);
+  p.w = D3(n.x / nn, n.y / nn, n.z / nn);
+  p.area = len;
+}
+
+void bake_quad(const rrt_hittable& h, int id, const Xform& X, BakedPrim& p) {
+  p.kind = PRIM_QUAD; p.id = id; p.mat = h.material;
+  p.Q = X.point(D3(h.a));
+  p.u = X.rot(D3(h.b));
+  p.v = X.rot(D3(h.c));
+  quad_derive(p);
+  D3 corners[4] = {p.Q, p.Q + p.u, p.Q + p.v, p.Q + p.u + p.v};  // quad.rs:50-54
+  for (int a = 0; a < 3; ++a) {
+    p.lo[a] = p.hi[a] = corners[0][a];
+    for (int k = 1; k < 4; ++k) { p.lo[a] = std::min(p.lo[a], corners[k][a]); p.hi[a] = std::max(p.hi[a], corners[k][a]); }
+    pad_axis(p.lo[a], p.hi[a]);
+  }
+}
+
+struct BakedMedium { int first, count, mat, id; double density; };
+
+struct Walker {
+  const rrt_scene_desc* d;
+  std::vector<BakedPrim> world;
+  std::vector<BakedPrim> boundary;
+  std::vector<BakedMedium> media;
+  std::string err;
+  int status = RRT_OK;
+
+  bool fail(int st, const std::string& m) { if (status == RRT_OK) { status = st; err = m; } return false; }
+
+  bool walk(int idx, const Xform& X, std::vector<BakedPrim>& out, int depth, bool in_boundary) {
+    if (idx < 0 || idx >= d->n_hittables) return fail(RRT_ERR_INVALID, "hittable index out of range");
+    if (depth > 64) return fail(RRT_ERR_INVALID, "scene graph deeper than 64 (cycle?)");
+    const rrt_hittable& h = d->hittables[idx];
+    switch (h.kind) {
+      case RRT_H_SPHERE: case RRT_H_QUAD: {
+        if (h.material < 0 || h.material >= d->n_materials)
+          return fail(RRT_ERR_INVALID, "primitive material index out of range");
+        BakedPrim p;
+        if (h.kind == RRT_H_SPHERE) bake_sphere(h, idx, X, p); else bake_quad(h, idx, X, p);
+        p.order = (int)out.size();
+        for (int a = 0; a < 3; ++a)
+          if (!std::isfinite(p.lo[a]) || !std::isfinite(p.hi[a]))
+            return fail(RRT_ERR_INVALID, "primitive with non-finite bounds (degenerate quad?)");
+        out.push_back(p);
+        return true;
+      }
+      case RRT_H_LIST: case RRT_H_BVH: {
+        if (h.first_child < 0 || h.n_children < 0 || h.first_child + h.n_children > d->n_children)
+          return fail(RRT_ERR_INVALID, "list children range out of bounds");
+        for (int k = 0; k < h.n_children; ++k)
+          if (!walk(d->children[h.first_child + k], X, out, depth + 1, in_boundary)) return false;
+        return true;
+      }
+      case RRT_H_TRANSLATE: {  // hittable.rs:86-93: p_parent = p_child + offset
+        Xform Y = X;
+        Y.t = X.point(D3(h.a));
+        return walk(h.first_child, Y, out, depth + 1, in_boundary);
+      }
+      case RRT_H_ROTATE_Y: {  // hittable.rs:107-112
+        double radians = h.a[0] * M_PI / 180.0;
+        double s2 = std::sin(radians), c2 = std::cos(radians);
+        Xform Y = X;
+        Y.c = X.c * c2 - X.s * s2;
+        Y.s = X.c * s2 + X.s * c2;
+        Y.rotated = true;
+        return walk(h.first_child, Y, out, depth + 1, in_boundary);
+      }
+      case RRT_H_CONSTANT_MEDIUM: {
+        if (in_boundary) return fail(RRT_ERR_UNSUPPORTED, "constant medium nested inside a medium boundary");
+        if (h.material < 0 || h.material >= d->n_materials)
+          return fail(RRT_ERR_INVALID, "medium phase material index out of range");
+        BakedMedium m;
+        m.first = (int)boundary.size(); m.mat = h.material; m.id = idx; m.density = h.a[0];
+        if (!walk(h.first_child, X, boundary, depth + 1, true)) return false;
+        m.count = (int)boundary.size() - m.first;
+        media.push_back(m);
+        return true;
+      }
+      default:
+        return fail(RRT_ERR_INVALID, "unknown hittable kind");
+    }
+  }
+};
+
+// ------------------------------------------------------------------------------------------------
+// BVH: binary, full-sweep SAH over the three axes (host, once per scene).  Not the reference's
+// 12-bucket builder (bvh.rs:34-156) — the closest hit does not depend on the tree.
+struct BNode {
+  double lo[3], hi[3];
+  int left = -1, right = -1;   // children (BNode indices) or -1
+  int first = 0, count = 0;    // leaf range in `order`
+};
+
+struct Builder {
+  const std::vector<BakedPrim>& P;
+  std::vector<int> order;
+  std::vector<BNode> nodes;
+  int max_leaf;
+  int max_depth_seen = 0;
+
+  Builder(const std::vector<BakedPrim>& p, int ml) : P(p), max_leaf(ml) {
+    order.resize(P.size());
+    for (size_t i = 0; i < P.size(); ++i) order[i] = (int)i;
+  }
+  static double area(const double* lo, const double* hi) {
+    double a = hi[0] - lo[0], b = hi[1] - lo[1], c = hi[2] - lo[2];
+    return 2.0 * (a * b + a * c + b * c);
+  }
+  void bounds(int first, int count, double* lo, double* hi) const {
+    for (int a = 0; a < 3; ++a) { lo[a] = std::numeric_limits<double>::infinity(); hi[a] = -lo[a]; }
+    for (int i = first; i < first + count; ++i) {
+      const BakedPrim& p = P[order[i]];
+      for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], p.lo[a]); hi[a] = std::max(hi[a], p.hi[a]); }
+    }
+  }
+  bool leaf_ok(int first, int count) const {
+    int ns = 0, nq = 0;
+    for (int i = first; i < first + count; ++i) (P[order[i]].kind == PRIM_SPHERE ? ns : nq)++;
+    return ns <= LEAF_MAX_PER_KIND && nq <= LEAF_MAX_PER_KIND;
+  }
+  int build(int first, int count, int depth) {
+    max_depth_seen = std::max(max_depth_seen, depth);
+    int me = (int)nodes.size();
+    nodes.push_back(BNode());
+    bounds(first, count, nodes[me].lo, nodes[me].hi);
+    nodes[me].first = first; nodes[me].count = count;
+    if (count <= 1 || (count <= max_leaf && depth >= 40)) return me;
+    double parent_area = area(nodes[me].lo, nodes[me].hi);
+    double best_cost = std::numeric_limits<double>::infinity();
+    int best_axis = -1, best_split = -1;
+    std::vector<double> right_area(count);
+    std::vector<int> tmp(order.begin() + first, order.begin() + first + count);
+    std::vector<int> best_order;
+    std::vector<int> sorted_by[3];
+    if (depth < 40) {
+      for (int axis = 0; axis < 3; ++axis) {
+        std::vector<int>& idx = sorted_by[axis];
+        idx = tmp;
+        std::stable_sort(idx.begin(), idx.end(), [&](int a, int b) {
+          return P[a].lo[axis] + P[a].hi[axis] < P[b].lo[axis] + P[b].hi[axis];
+        });
+        double lo[3], hi[3];
+        for (int a = 0; a < 3; ++a) { lo[a] = std::numeric_limits<double>::infinity(); hi[a] = -lo[a]; }
+        for (int i = count - 1; i > 0; --i) {
+          const BakedPrim& p = P[idx[i]];
+          for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], p.lo[a]); hi[a] = std::max(hi[a], p.hi[a]); }
+          right_area[i] = area(lo, hi);
+        }
+        for (int a = 0; a < 3; ++a) { lo[a] = std::numeric_limits<double>::infinity(); hi[a] = -lo[a]; }
+        for (int i = 1; i < count; ++i) {
+          const BakedPrim& p = P[idx[i - 1]];
+          for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], p.lo[a]); hi[a] = std::max(hi[a], p.hi[a]); }
+          double cost = area(lo, hi) * i + right_area[i] * (count - i);
+          if (cost < best_cost) { best_cost = cost; best_axis = axis; best_split = i; }
+        }
+      }
+      if (best_axis >= 0) best_order.swap(sorted_by[best_axis]);
+    }
+    // leaf cost = count intersections; split cost = 1 traversal step + SAH-weighted children
+    bool can_leaf = count <= max_leaf && leaf_ok(first, count);
+    if (best_axis >= 0 && parent_area > 0) {
+      double split_cost = 1.0 + best_cost / parent_area;
+      if (can_leaf && (double)count <= split_cost) return me;
+    } else if (can_leaf) {
+      return me;
+    }
+    int mid;
+    if (best_axis < 0) {  // too deep or degenerate: median split on the longest axis
+      int axis = 0;
+      double ext = -1;
+      for (int a = 0; a < 3; ++a) if (nodes[me].hi[a] - nodes[me].lo[a] > ext) { ext = nodes[me].hi[a] - nodes[me].lo[a]; axis = a; }
+      best_order = tmp;
+      std::stable_sort(best_order.begin(), best_order.end(), [&](int a, int b) {
+        return P[a].lo[axis] + P[a].hi[axis] < P[b].lo[axis] + P[b].hi[axis];
+      });
+      mid = count / 2;
+    } else {
+      mid = best_split;
+    }
+    std::copy(best_order.begin(), best_order.end(), order.begin() + first);
+    int l = build(first, mid, depth + 1);
+    int r = build(first + mid, count - mid, depth + 1);
+    nodes[me].left = l; nodes[me].right = r;
+    return me;
+  }
+};
+
+inline float round_down(double v) {
+  float f = (float)v;
+  if ((double)f > v) f = std::nextafterf(f, -std::numeric_limits<float>::infinity());
+  return f;
+}
+inline float round_up(double v) {
+  float f = (float)v;
+  if ((double)f < v) f = std::nextafterf(f, std::numeric_limits<float>::infinity());
+  return f;
+}
+inline float as_float(int i) { float f; std::memcpy(&f, &i, 4); return f; }
+inline float4 f4(double a, double b, double c, double d) { float4 r; r.x = (float)a; r.y = (float)b; r.z = (float)c; r.w = (float)d; return r; }
+inline float4 i4(int a, int b, int c, int d) { float4 r; r.x = as_float(a); r.y = as_float(b); r.z = as_float(c); r.w = as_float(d); return r; }
+
+void emit_prim32(const BakedPrim& p, std::vector<float4>& out) {
+  if (p.kind == PRIM_SPHERE) {
+    out.push_back(f4(p.c0.x, p.c0.y, p.c0.z, p.r));
+    out.push_back(f4(p.dc.x, p.dc.y, p.dc.z, p.r > 0 ? 1.0 / p.r : 0.0));
+    out.push_back(i4(p.mat, p.id, p.order, p.flags));
+    out.push_back(f4(p.uvcos, p.uvsin, 0, 0));
+  } else {
+    D3 A = cross(p.v, p.w), B = cross(p.w, p.u);
+    out.push_back(f4(p.n.x, p.n.y, p.n.z, p.d));
+    out.push_back(f4(A.x, A.y, A.z, -dot(p.Q, A)));
+    out.push_back(f4(B.x, B.y, B.z, -dot(p.Q, B)));
+    out.push_back(i4(p.mat, p.id, p.order, p.flags));
+  }
+}
+void emit_prim64(const BakedPrim& p, std::vector<double>& out) {
+  double q[16] = {0};
+  if (p.kind == PRIM_SPHERE) {
+    q[0] = p.c0.x; q[1] = p.c0.y; q[2] = p.c0.z; q[3] = p.r; q[4] = p.dc.x; q[5] = p.dc.y; q[6] = p.dc.z;
+  } else {
+    q[0] = p.n.x; q[1] = p.n.y; q[2] = p.n.z; q[3] = p.d;
+    q[4] = p.Q.x; q[5] = p.Q.y; q[6] = p.Q.z;
+    q[7] = p.u.x; q[8] = p.u.y; q[9] = p.u.z;
+    q[10] = p.v.x; q[11] = p.v.y; q[12] = p.v.z;
+    q[13] = p.w.x; q[14] = p.w.y; q[15] = p.w.z;
+  }
+  out.insert(out.end(), q, q + 16);
+}
+
+// conservative f32 box: outward rounding plus a relative pad that covers the f32 slab arithmetic
+void box32(const double* lo, const double* hi, float* flo, float* fhi) {
+  for (int a = 0; a < 3; ++a) {
+    double m = std::max(std::fabs(lo[a]), std::fabs(hi[a]));
+    double pad = 4e-7 * m + 1e-7 * (hi[a] - lo[a]);
+    flo[a] = round_down(lo[a] - pad);
+    fhi[a] = round_up(hi[a] + pad);
+  }
+}
+
+bool tex_needs_ok(const rrt_scene_desc* d, int t, int depth) {
+  if (t < 0) return true;
+  if (t >= d->n_textures || depth > 8) return false;
+  const rrt_texture& x = d->textures[t];
+  if (x.kind == RRT_T_CHECKER) return tex_needs_ok(d, x.even, depth + 1) && tex_needs_ok(d, x.odd, depth + 1) && x.even >= 0 && x.odd >= 0;
+  if (x.kind == RRT_T_IMAGE) return x.image >= 0 && x.image < d->n_images;
+  if (x.kind == RRT_T_NOISE) return x.perlin >= 0 && x.perlin < d->n_perlins;
+  return x.kind == RRT_T_SOLID;
+}
+
+}  // namespace
+
+int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, int single_leaf_max, int max_leaf) {
+  if (!desc) { err = "scene description is null"; return RRT_ERR_INVALID; }
+  if (desc->n_hittables < 0 || (desc->n_hittables > 0 && !desc->hittables) ||
+      (desc->n_children > 0 && !desc->children) || (desc->n_materials > 0 && !desc->materials) ||
+      (desc->n_textures > 0 && !desc->textures) || (desc->n_images > 0 && !desc->images) ||
+      (desc->n_perlins > 0 && !desc->perlins)) {
+    err = "scene description has a null array with a positive count"; return RRT_ERR_INVALID;
+  }
+  Walker w; w.d = desc;
+  Xform I;
+  if (desc->n_hittables > 0 || desc->world >= 0) {
+    if (!w.walk(desc->world, I, w.world, 0, false)) { err = w.err; return w.status; }
+  }
+  // ---- materials / textures / images / perlin
+  for (int i = 0; i < desc->n_materials; ++i) {
+    const rrt_material& m = desc->materials[i];
+    if (m.kind < RRT_M_LAMBERTIAN || m.kind > RRT_M_EMPTY) { err = "unknown material kind"; return RRT_ERR_INVALID; }
+    bool textured = m.kind == RRT_M_LAMBERTIAN || m.kind == RRT_M_DIFFUSE_LIGHT || m.kind == RRT_M_ISOTROPIC;
+    if (textured && (m.texture < 0 || !tex_needs_ok(desc, m.texture, 0))) {
+      err = "material texture index invalid"; return RRT_ERR_INVALID;
+    }
+    DevMaterial dm; std::memset(&dm, 0, sizeof dm);
+    dm.kind = m.kind; dm.tex = textured ? m.texture : -1;
+    dm.fuzz = (float)m.fuzz; dm.ior = (float)m.refraction_index;
+    dm.albedo = f4(m.albedo[0], m.albedo[1], m.albedo[2], 0);
+    if (textured && desc->textures[m.texture].kind == RRT_T_SOLID) {  // SolidColor fast path
+      const rrt_texture& t = desc->textures[m.texture];
+      dm.albedo = f4(t.color[0], t.color[1], t.color[2], 0);
+      dm.tex = -1;
+    }
+    out.materials.push_back(dm);
+  }
+  for (int i = 0; i < desc->n_textures; ++i) {
+    const rrt_texture& t = desc->textures[i];
+    DevTexture dt; std::memset(&dt, 0, sizeof dt);
+    dt.kind = t.kind;
+    switch (t.kind) {
+      case RRT_T_SOLID: dt.v = f4(t.color[0], t.color[1], t.color[2], 0); break;
+      case RRT_T_CHECKER: dt.a = t.even; dt.b = t.odd; dt.v = f4(0, 0, 0, 1.0 / t.scale); break;  // texture.rs:51
+      case RRT_T_IMAGE: dt.a = t.image; break;
+      case RRT_T_NOISE: dt.a = t.perlin; dt.v = f4(0, 0, 0, t.scale); break;
+      default: err = "unknown texture kind"; return RRT_ERR_INVALID;
+    }
+    out.textures.push_back(dt);
+  }
+  for (int i = 0; i < desc->n_images; ++i) {
+    const rrt_image& im = desc->images[i];
+    DevImage di; di.width = im.rgb ? im.width : 0; di.height = im.rgb ? im.height : 0;
+    di.offset = (int)(out.texels.size() / 4); di.pad = 0;
+    if (im.rgb) {
+      size_t n = (size_t)im.width * im.height;
+      size_t base = out.texels.size();
+      out.texels.resize(base + n * 4);
+      for (size_t k = 0; k < n; ++k) {
+        out.texels[base + 4 * k + 0] = im.rgb[3 * k + 0];
+        out.texels[base + 4 * k + 1] = im.rgb[3 * k + 1];
+        out.texels[base + 4 * k + 2] = im.rgb[3 * k + 2];
+        out.texels[base + 4 * k + 3] = 255;
+      }
+    }
+    out.images.push_back(di);
+  }
+  for (int i = 0; i < desc->n_perlins; ++i) {
+    const rrt_perlin& p = desc->perlins[i];
+    out.perlins.emplace_back();
+    DevPerlin& dp = out.perlins.back();
+    for (int k = 0; k < 256; ++k) {
+      dp.randvec[k] = f4(p.randvec[k][0], p.randvec[k][1], p.randvec[k][2], 0);
+      dp.perm[0][k] = (uint8_t)(p.perm_x[k] & 255);
+      dp.perm[1][k] = (uint8_t)(p.perm_y[k] & 255);
+      dp.perm[2][k] = (uint8_t)(p.perm_z[k] & 255);
+    }
+  }
+  // ---- media boundaries (outside the BVH; spheres first, then quads, per medium)
+  for (const BakedMedium& m : w.media) {
+    DevMedium dm; std::memset(&dm, 0, sizeof dm);
+    dm.first = (int)(out.bprims.size() / 4);
+    dm.mat = m.mat; dm.id = m.id;
+    dm.neg_inv_density = (float)(-1.0 / m.density);  // constant_medium.rs:26
+    for (int pass = 0; pass < 2; ++pass)
+      for (int k = m.first; k < m.first + m.count; ++k)
+        if (w.boundary[k].kind == pass) { emit_prim32(w.boundary[k], out.bprims); (pass == 0 ? dm.nsph : dm.nquad)++; }
+    out.media.push_back(dm);
+  }
+  // ---- lights (book 3): a list of spheres/quads, or a single one
+  if (desc->lights >= 0) {
+    if (desc->lights >= desc->n_hittables) { err = "lights index out of range"; return RRT_ERR_INVALID; }
+    std::vector<int> ids;
+    const rrt_hittable& L = desc->hittables[desc->lights];
+    if (L.kind == RRT_H_LIST) {
+      if (L.first_child < 0 || L.first_child + L.n_children > desc->n_children) { err = "lights children out of range"; return RRT_ERR_INVALID; }
+      for (int k = 0; k < L.n_children; ++k) ids.push_back(desc->children[L.first_child + k]);
+    } else {
+      ids.push_back(desc->lights);
+    }
+    for (int id : ids) {
+      if (id < 0 || id >= desc->n_hittables) { err = "light index out of range"; return RRT_ERR_INVALID; }
+      const rrt_hittable& h = desc->hittables[id];
+      DevLight dl; std::memset(&dl, 0, sizeof dl);
+      BakedPrim p;
+      if (h.kind == RRT_H_SPHERE) {
+        bake_sphere(h, id, I, p);
+        dl.kind = 0; dl.a = f4(p.c0.x, p.c0.y, p.c0.z, p.r);
+      } else if (h.kind == RRT_H_QUAD) {
+        bake_quad(h, id, I, p);
+        D3 A = cross(p.v, p.w), B = cross(p.w, p.u);
+        dl.kind = 1;
+        dl.a = f4(p.n.x, p.n.y, p.n.z, p.d);
+        dl.b = f4(A.x, A.y, A.z, -dot(p.Q, A));
+        dl.c = f4(B.x, B.y, B.z, -dot(p.Q, B));
+        dl.q = f4(p.Q.x, p.Q.y, p.Q.z, p.area);
+        dl.u = f4(p.u.x, p.u.y, p.u.z, 0);
+        dl.v = f4(p.v.x, p.v.y, p.v.z, 0);
+      } else {
+        dl.kind = 2;  // trait defaults: pdf_value 0, random (1,0,0)  (hittable.rs:58-64)
+      }
+      out.lights.push_back(dl);
+    }
+  }
+  // ---- BVH over the world prims
+  const std::vector<BakedPrim>& P = w.world;
+  out.n_prims = (int)P.size();
+  for (const BakedPrim& p : P) if (p.kind == PRIM_SPHERE && (p.dc.x != 0 || p.dc.y != 0 || p.dc.z != 0)) out.has_motion = 1;
+  for (const BakedPrim& p : w.boundary) if (p.kind == PRIM_SPHERE && (p.dc.x != 0 || p.dc.y != 0 || p.dc.z != 0)) out.has_motion = 1;
+  if (P.empty()) { out.root_ref = make_leaf_ref(0, 0, 0); return RRT_OK; }
+  int ns = 0, nq = 0;
+  for (const BakedPrim& p : P) (p.kind == PRIM_SPHERE ? ns : nq)++;
+  bool single = (int)P.size() <= single_leaf_max && ns <= LEAF_MAX_PER_KIND && nq <= LEAF_MAX_PER_KIND;
+  Builder B(P, single ? (int)P.size() : max_leaf);
+  int root = 0;
+  if (single) {
+    B.nodes.push_back(BNode());
+    B.bounds(0, (int)P.size(), B.nodes[0].lo, B.nodes[0].hi);
+    B.nodes[0].first = 0; B.nodes[0].count = (int)P.size();
+  } else {
+    root = B.build(0, (int)P.size(), 0);
+  }
+  out.bvh_depth = B.max_depth_seen;
+  // leaf -> contiguous prim run (spheres first, then quads); prims emitted in `order` sequence
+  std::vector<int> leaf_ref(B.nodes.size(), 0);
+  {
+    // emit prims leaf by leaf in B.order sequence (DFS), reordering within the leaf by kind
+    std::vector<int> first_of(B.nodes.size(), -1);
+    int emitted = 0;
+    // B.order ranges of leaves are disjoint and cover [0,n); walk nodes, leaves own [first,count)
+    std::vector<int> leaves;
+    for (size_t i = 0; i < B.nodes.size(); ++i) if (B.nodes[i].left < 0) leaves.push_back((int)i);
+    std::sort(leaves.begin(), leaves.end(), [&](int a, int b) { return B.nodes[a].first < B.nodes[b].first; });
+    for (int li : leaves) {
+      const BNode& n = B.nodes[li];
+      int s = 0, q = 0;
+      for (int pass = 0; pass < 2; ++pass)
+        for (int k = n.first; k < n.first + n.count; ++k) {
+          const BakedPrim& p = P[B.order[k]];
+          if (p.kind == pass) { emit_prim32(p, out.prims); emit_prim64(p, out.prims64); (pass == 0 ? s : q)++; }
+        }
+      leaf_ref[li] = make_leaf_ref(emitted, s, q);
+      emitted += n.count;
+    }
+  }
+  if (B.nodes[root].left < 0) { out.root_ref = leaf_ref[root]; return RRT_OK; }
+  // inner nodes breadth-first
+  std::vector<int> inner_index(B.nodes.size(), -1);
+  std::vector<int> bfs;
+  {
+    std::queue<int> q; q.push(root);
+    while (!q.empty()) {
+      int n = q.front(); q.pop();
+      inner_index[n] = (int)bfs.size(); bfs.push_back(n);
+      int ch[2] = {B.nodes[n].left, B.nodes[n].right};
+      for (int c : ch) if (B.nodes[c].left >= 0) q.push(c);
+    }
+  }
+  for (int n : bfs) {
+    const BNode& l = B.nodes[B.nodes[n].left];
+    const BNode& r = B.nodes[B.nodes[n].right];
+    float llo[3], lhi[3], rlo[3], rhi[3];
+    box32(l.lo, l.hi, llo, lhi); box32(r.lo, r.hi, rlo, rhi);
+    int ref0 = l.left >= 0 ? inner_index[B.nodes[n].left] : leaf_ref[B.nodes[n].left];
+    int ref1 = r.left >= 0 ? inner_index[B.nodes[n].right] : leaf_ref[B.nodes[n].right];
+    float4 a; a.x = llo[0]; a.y = lhi[0]; a.z = llo[1]; a.w = lhi[1];
+    float4 b; b.x = rlo[0]; b.y = rhi[0]; b.z = rlo[1]; b.w = rhi[1];
+    float4 c; c.x = llo[2]; c.y = lhi[2]; c.z = rlo[2]; c.w = rhi[2];
+    out.nodes.push_back(a); out.nodes.push_back(b); out.nodes.push_back(c);
+    out.nodes.push_back(i4(ref0, ref1, 0, 0));
+  }
+  out.root_ref = 0;
+  return RRT_OK;
+}
+
+// Camera::initialize, the_rest_of_your_life/camera.rs:108-154 (book 1/2 copies are the same apart
+// from sqrt_spp).  All f64; the f32 block keeps pixel00 relative to the centre.
+int camera_initialize(const rrt_camera* cam, DevCamera& c32, DevCamera64& c64) {
+  int image_height = (int)((double)cam->image_width / cam->aspect_ratio);
+  if (image_height < 1) image_height = 1;
+  int sqrt_spp = (int)std::sqrt((double)cam->samples_per_pixel);
+  double recip_sqrt_spp = 1.0 / (double)sqrt_spp;
+  D3 center(cam->lookfrom);
+  double theta = cam->vfov * M_PI / 180.0;
+  double h = std::tan(theta / 2.0);
+  double viewport_height = 2.0 * h * cam->focus_dist;
+  double viewport_width = viewport_height * ((double)cam->image_width / (double)image_height);
+  D3 wv = D3(cam->lookfrom) - D3(cam->lookat);
+  double wl = std::sqrt(dot(wv, wv));
+  D3 w(wv.x / wl, wv.y / wl, wv.z / wl);
+  D3 uc = cross(D3(cam->vup), w);
+  double ul = std::sqrt(dot(uc, uc));
+  D3 u(uc.x / ul, uc.y / ul, uc.z / ul);
+  D3 v = cross(w, u);
+  D3 viewport_u = viewport_width * u;
+  D3 viewport_v = viewport_height * D3(-v.x, -v.y, -v.z);
+  D3 du(viewport_u.x / cam->image_width, viewport_u.y / cam->image_width, viewport_u.z / cam->image_width);
+  D3 dv(viewport_v.x / image_height, viewport_v.y / image_height, viewport_v.z / image_height);
+  D3 half_u(viewport_u.x / 2.0, viewport_u.y / 2.0, viewport_u.z / 2.0);
+  D3 half_v(viewport_v.x / 2.0, viewport_v.y / 2.0, viewport_v.z / 2.0);
+  D3 upper_left = center - (cam->focus_dist * w) - half_u - half_v;
+  D3 pixel00 = upper_left + 0.5 * (du + dv);
+  double defocus_radius = cam->focus_dist * std::tan((cam->defocus_angle / 2.0) * M_PI / 180.0);
+  D3 ddu = defocus_radius * u, ddv = defocus_radius * v;  // u * r in the reference; commutative
+  D3 rel = pixel00 - center;
+  c32.cx = (float)center.x; c32.cy = (float)center.y; c32.cz = (float)center.z;
+  c32.p00x = (float)rel.x; c32.p00y = (float)rel.y; c32.p00z = (float)rel.z;
+  c32.dux = (float)du.x; c32.duy = (float)du.y; c32.duz = (float)du.z;
+  c32.dvx = (float)dv.x; c32.dvy = (float)dv.y; c32.dvz = (float)dv.z;
+  c32.ddux = (float)ddu.x; c32.dduy = (float)ddu.y; c32.dduz = (float)ddu.z;
+  c32.ddvx = (float)ddv.x; c32.ddvy = (float)ddv.y; c32.ddvz = (float)ddv.z;
+  c32.bgx = (float)cam->background[0]; c32.bgy = (float)cam->background[1]; c32.bgz = (float)cam->background[2];
+  c32.recip_sqrt_spp = (float)recip_sqrt_spp;
+  c32.sqrt_spp = sqrt_spp;
+  c32.defocus = cam->defocus_angle > 0.0 ? 1 : 0;
+  for (int a = 0; a < 3; ++a) { c64.c[a] = center[a]; c64.p00[a] = pixel00[a]; c64.du[a] = du[a]; c64.dv[a] = dv[a]; }
+  return image_height;
+}
+
+}  // namespace rrt

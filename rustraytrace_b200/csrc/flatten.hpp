@@ -1,0 +1,40 @@
+// flatten.hpp — host side of rrt_scene_create: rrt_scene_desc (pointer-tree shaped, f64) ->
+// flat world-space primitives + our own BVH + SoA tables.  Replaces, for the GPU, what the
+// reference does with Arc trees: BvhNode::new (bvh.rs:16-156), Translate/RotateY wrappers
+// (hittable.rs:73-178), HittableList nesting (hittable_list.rs), make_box lists (quad.rs:112-134).
+#pragma once
+#include <string>
+#include <vector>
+
+#include "../../include/rrt.h"
+#include "device_types.h"
+
+namespace rrt {
+
+struct FlatScene {
+  std::vector<float4> prims;      // 4 per prim
+  std::vector<double> prims64;    // 16 per prim
+  std::vector<float4> nodes;      // 4 per inner node
+  std::vector<float4> bprims;     // 4 per medium-boundary prim
+  std::vector<DevMaterial> materials;
+  std::vector<DevTexture> textures;
+  std::vector<DevImage> images;
+  std::vector<unsigned char> texels;  // uchar4 pool
+  std::vector<DevPerlin> perlins;
+  std::vector<DevMedium> media;
+  std::vector<DevLight> lights;
+  int root_ref = -1;
+  int n_prims = 0;
+  int has_motion = 0;
+  int bvh_depth = 0;
+};
+
+// Returns RRT_OK or a negative rrt_status with `err` filled.
+// single_leaf_max: scenes with at most this many primitives become one root leaf (brute force).
+int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err,
+                  int single_leaf_max = 16, int max_leaf = 4);
+
+// Camera::initialize (camera.rs:108-154) -> device camera blocks.  Returns image height.
+int camera_initialize(const rrt_camera* cam, DevCamera& c32, DevCamera64& c64);
+
+}  // namespace rrt

@@ -1,0 +1,318 @@
+// intersect.cuh — ray/primitive tests and the stack BVH traversal.
+//
+// What it restates (hot loops 3-4 of SURVEY.md §3.1):
+//   Sphere::hit        the_rest_of_your_life/sphere.rs:69-96   (open interval: Interval::surrounds)
+//   Quad::hit          the_rest_of_your_life/quad.rs:64-91     (closed interval: Interval::contains)
+//   Aabb::hit          the_rest_of_your_life/aabb.rs:52-84     (slab test)
+//   BvhNode::hit       the_rest_of_your_life/bvh.rs:159-172    (closest hit below the node)
+//   HittableList::hit  the_rest_of_your_life/hittable_list.rs:42-54
+// Translate/RotateY (hittable.rs:86-173) do not appear: instances are baked to world space on the
+// host (flatten.cpp), which leaves t unchanged because the maps are rigid.
+//
+// Equal-t rule.  The reference's result at an exact tie is decided by list order plus the
+// open/closed interval asymmetry: a later quad replaces an equal-t hit (contains), a later sphere
+// does not (surrounds).  Traversal order here is different, so the rule is applied explicitly on
+// the primitives' construction order: quad beats sphere; between quads the later wins; between
+// spheres the earlier wins.
+#pragma once
+#include "device_types.h"
+#include "vecmath.cuh"
+
+namespace rrt {
+
+#define RRT_STACK 64
+#define PRIM_QUAD_BIT 0x40000000
+
+struct Ray32 {
+  V3f o, d;
+  float tm;
+};
+
+struct Hit32 {
+  float t;   // closest so far (starts at +inf)
+  int prim;  // flat prim index | PRIM_QUAD_BIT, or -1
+};
+
+__device__ inline int prim_order(const float4* prims, int prim) {
+  int idx = prim & ~PRIM_QUAD_BIT;
+  float4 m = ldg4(prims + 4 * idx + ((prim & PRIM_QUAD_BIT) ? 3 : 2));
+  return __float_as_int(m.z);
+}
+
+// cand beats the current best at equal t?
+__device__ inline bool tie_accept(const float4* prims, int cand, int best) {
+  if (best < 0) return true;
+  bool cq = cand & PRIM_QUAD_BIT, bq = best & PRIM_QUAD_BIT;
+  if (cq != bq) return cq;
+  int co = prim_order(prims, cand), bo = prim_order(prims, best);
+  return cq ? (co > bo) : (co < bo);
+}
+
+// Sphere::hit in f32.  The discriminant is formed from the component of oc perpendicular to the
+// ray (r^2 - |oc - (h/a) d|^2 = discriminant / a), which avoids the cancellation of
+// |oc|^2 - r^2 for small far spheres; same roots as sphere.rs:71-89.
+// skip: the sphere this ray starts on — only its far root is legal, and only when heading inward.
+__device__ inline void sphere_hit32(const float4* __restrict__ prims, int i, const Ray32& r, float a,
+                                    float inv_a, float tmin, int skip, bool motion, Hit32& h) {
+  float4 p0 = ldg4(prims + 4 * i);
+  V3f c(p0.x, p0.y, p0.z);
+  if (motion) {
+    float4 p1 = ldg4(prims + 4 * i + 1);
+    c = c + r.tm * V3f(p1.x, p1.y, p1.z);  // center.at(time), sphere.rs:70
+  }
+  V3f oc = c - r.o;
+  float hh = dot(r.d, oc);
+  float k = hh * inv_a;
+  V3f perp = oc - k * r.d;
+  float disc = p0.w * p0.w - dot(perp, perp);
+  if (disc < 0.0f) return;
+  float sq = sqrtf(disc * a);
+  float root;
+  if (i == skip) {
+    if (hh <= 0.0f) return;
+    root = (hh + sq) * inv_a;
+    if (!(root > tmin && root <= h.t)) return;
+  } else {
+    root = (hh - sq) * inv_a;
+    if (!(root > tmin && root <= h.t)) {
+      root = (hh + sq) * inv_a;
+      if (!(root > tmin && root <= h.t)) return;
+    }
+  }
+  if (root == h.t && !tie_accept(prims, i, h.prim)) return;
+  h.t = root;
+  h.prim = i;
+}
+
+// Quad::hit in f32.  alpha = w.(hp x v) = p.A + a0, beta = w.(u x hp) = p.B + b0 (quad.rs:76-79).
+__device__ inline void quad_hit32(const float4* __restrict__ prims, int i, const Ray32& r, float tmin,
+                                  int skip, Hit32& h) {
+  if (i == skip) return;  // a ray leaving a plane cannot meet it again (reference: t ~ 1e-16 < 0.001)
+  float4 p0 = ldg4(prims + 4 * i);
+  V3f n(p0.x, p0.y, p0.z);
+  float denom = dot(n, r.d);
+  if (fabsf(denom) < 1e-8f) return;  // quad.rs:67
+  float t = (p0.w - dot(n, r.o)) / denom;
+  if (!(t >= tmin && t <= h.t)) return;  // contains, quad.rs:72
+  V3f p = r.o + t * r.d;
+  float4 p1 = ldg4(prims + 4 * i + 1);
+  float alpha = dot(p, V3f(p1.x, p1.y, p1.z)) + p1.w;
+  if (!(alpha >= 0.0f && alpha <= 1.0f)) return;  // is_interior, quad.rs:51-60
+  float4 p2 = ldg4(prims + 4 * i + 2);
+  float beta = dot(p, V3f(p2.x, p2.y, p2.z)) + p2.w;
+  if (!(beta >= 0.0f && beta <= 1.0f)) return;
+  if (t == h.t && !tie_accept(prims, i | PRIM_QUAD_BIT, h.prim)) return;
+  h.t = t;
+  h.prim = i | PRIM_QUAD_BIT;
+}
+
+// One leaf: a contiguous run, spheres first.  ~ref = (first << 8) | (nsph << 4) | nquad.
+__device__ inline void leaf_hit32(const float4* __restrict__ prims, int leaf, const Ray32& r, float a,
+                                  float inv_a, float tmin, int skip, bool motion, Hit32& h) {
+  int first = leaf >> 8, ns = (leaf >> 4) & 15, nq = leaf & 15;
+  for (int k = 0; k < ns; ++k) sphere_hit32(prims, first + k, r, a, inv_a, tmin, skip, motion, h);
+  first += ns;
+  for (int k = 0; k < nq; ++k) quad_hit32(prims, first + k, r, tmin, skip, h);
+}
+
+__device__ inline float safe_rcp(float d) {
+  // a zero direction component would turn the slab products into NaN (0 * inf); aabb.rs:58 has
+  // the same hazard in f64 but never meets an exact zero.  Clamp instead.
+  float ad = fabsf(d);
+  return 1.0f / (ad > 1e-30f ? d : copysignf(1e-30f, d));
+}
+
+// World::hit for the render kernel: closest hit in (tmin, +inf).
+// s_nodes: leading n_smem nodes staged in shared memory (breadth-first prefix).
+__device__ inline void world_hit32(const DevScene& S, const float4* __restrict__ s_nodes, const Ray32& r,
+                                   float tmin, int skip, Hit32& h) {
+  const float a = dot(r.d, r.d);
+  const float inv_a = 1.0f / a;
+  const bool motion = S.has_motion != 0;
+  int cur = S.root_ref;
+  if (cur < 0) {  // the whole scene is one leaf: brute force, uniform control flow
+    leaf_hit32(S.prims, ~cur, r, a, inv_a, tmin, skip, motion, h);
+    return;
+  }
+  const float idx = safe_rcp(r.d.x), idy = safe_rcp(r.d.y), idz = safe_rcp(r.d.z);
+  const float oodx = r.o.x * idx, oody = r.o.y * idy, oodz = r.o.z * idz;
+  int stack[RRT_STACK];
+  int sp = 0;
+  const int n_smem = S.smem_nodes;
+  for (;;) {
+    if (cur >= 0) {
+      float4 n0, n1, n2, n3;
+      if (cur < n_smem) {
+        n0 = s_nodes[4 * cur]; n1 = s_nodes[4 * cur + 1]; n2 = s_nodes[4 * cur + 2]; n3 = s_nodes[4 * cur + 3];
+      } else {
+        const float4* g = S.nodes + 4 * cur;
+        n0 = ldg4(g); n1 = ldg4(g + 1); n2 = ldg4(g + 2); n3 = ldg4(g + 3);
+      }
+      // Aabb::hit (aabb.rs:52-84) for both children; t = lo * (1/d) - o * (1/d)
+      float c0x0 = fmaf(n0.x, idx, -oodx), c0x1 = fmaf(n0.y, idx, -oodx);
+      float c0y0 = fmaf(n0.z, idy, -oody), c0y1 = fmaf(n0.w, idy, -oody);
+      float c0z0 = fmaf(n2.x, idz, -oodz), c0z1 = fmaf(n2.y, idz, -oodz);
+      float c1x0 = fmaf(n1.x, idx, -oodx), c1x1 = fmaf(n1.y, idx, -oodx);
+      float c1y0 = fmaf(n1.z, idy, -oody), c1y1 = fmaf(n1.w, idy, -oody);
+      float c1z0 = fmaf(n2.z, idz, -oodz), c1z1 = fmaf(n2.w, idz, -oodz);
+      float near0 = fmaxf(fmaxf(fminf(c0x0, c0x1), fminf(c0y0, c0y1)), fmaxf(fminf(c0z0, c0z1), tmin));
+      float far0 = fminf(fminf(fmaxf(c0x0, c0x1), fmaxf(c0y0, c0y1)), fminf(fmaxf(c0z0, c0z1), h.t));
+      float near1 = fmaxf(fmaxf(fminf(c1x0, c1x1), fminf(c1y0, c1y1)), fmaxf(fminf(c1z0, c1z1), tmin));
+      float far1 = fminf(fminf(fmaxf(c1x0, c1x1), fmaxf(c1y0, c1y1)), fminf(fmaxf(c1z0, c1z1), h.t));
+      bool hit0 = near0 <= far0 * 1.0000004f;
+      bool hit1 = near1 <= far1 * 1.0000004f;
+      int r0 = __float_as_int(n3.x), r1 = __float_as_int(n3.y);
+      if (hit0 && hit1) {
+        if (near1 < near0) { int t = r0; r0 = r1; r1 = t; }
+        if (sp < RRT_STACK) stack[sp++] = r1;
+        cur = r0;
+        continue;
+      }
+      if (hit0) { cur = r0; continue; }
+      if (hit1) { cur = r1; continue; }
+    } else {
+      leaf_hit32(S.prims, ~cur, r, a, inv_a, tmin, skip, motion, h);
+    }
+    if (sp == 0) break;
+    cur = stack[--sp];
+  }
+}
+
+// Closest hit of a medium boundary run in [lo, hi] for quads / (lo, hi) for spheres
+// (boundary.hit(r, interval), constant_medium.rs:41-42).  Returns t or -1 flagged by `found`.
+__device__ inline bool boundary_hit32(const float4* __restrict__ bprims, const DevMedium& m, const Ray32& r,
+                                      float a, float inv_a, float lo, float hi, bool motion, float& t_out) {
+  bool found = false;
+  float best = hi;
+  int first = m.first;
+  for (int k = 0; k < m.nsph; ++k) {
+    int i = first + k;
+    float4 p0 = ldg4(bprims + 4 * i);
+    V3f c(p0.x, p0.y, p0.z);
+    if (motion) { float4 p1 = ldg4(bprims + 4 * i + 1); c = c + r.tm * V3f(p1.x, p1.y, p1.z); }
+    V3f oc = c - r.o;
+    float hh = dot(r.d, oc);
+    V3f perp = oc - (hh * inv_a) * r.d;
+    float disc = p0.w * p0.w - dot(perp, perp);
+    if (disc < 0.0f) continue;
+    float sq = sqrtf(disc * a);
+    float root = (hh - sq) * inv_a;
+    if (!(root > lo && root < best)) {
+      root = (hh + sq) * inv_a;
+      if (!(root > lo && root < best)) continue;
+    }
+    best = root; found = true;
+  }
+  first += m.nsph;
+  for (int k = 0; k < m.nquad; ++k) {
+    int i = first + k;
+    float4 p0 = ldg4(bprims + 4 * i);
+    V3f n(p0.x, p0.y, p0.z);
+    float denom = dot(n, r.d);
+    if (fabsf(denom) < 1e-8f) continue;
+    float t = (p0.w - dot(n, r.o)) / denom;
+    if (!(t >= lo && t <= best)) continue;
+    V3f p = r.o + t * r.d;
+    float4 p1 = ldg4(bprims + 4 * i + 1);
+    float alpha = dot(p, V3f(p1.x, p1.y, p1.z)) + p1.w;
+    if (!(alpha >= 0.0f && alpha <= 1.0f)) continue;
+    float4 p2 = ldg4(bprims + 4 * i + 2);
+    float beta = dot(p, V3f(p2.x, p2.y, p2.z)) + p2.w;
+    if (!(beta >= 0.0f && beta <= 1.0f)) continue;
+    best = t; found = true;
+  }
+  t_out = best;
+  return found;
+}
+
+// ------------------------------------------------------------------------------------------------
+// f64 probe path: the reference's formulas verbatim on the f64 prim records.
+struct Hit64 {
+  double t;
+  int prim;  // flat index | PRIM_QUAD_BIT, -1 none
+};
+
+__device__ inline void sphere_hit64(const double* __restrict__ q, int i, V3d o, V3d d, double tmin,
+                                    const float4* prims, Hit64& h) {
+  const double* s = q + 16 * i;
+  V3d c(s[0], s[1], s[2]);  // probe time is 0: center.at(0) = center0
+  V3d oc = c - o;
+  double a = dot(d, d);
+  double hh = dot(d, oc);
+  double cc = dot(oc, oc) - s[3] * s[3];
+  double disc = hh * hh - a * cc;  // sphere.rs:76
+  if (disc < 0.0) return;
+  double sq = sqrt(disc);
+  double root = (hh - sq) / a;
+  if (!(root > tmin && root <= h.t)) {
+    root = (hh + sq) / a;
+    if (!(root > tmin && root <= h.t)) return;
+  }
+  if (root == h.t && !tie_accept(prims, i, h.prim)) return;
+  h.t = root; h.prim = i;
+}
+
+__device__ inline void quad_hit64(const double* __restrict__ q, int i, V3d o, V3d d, double tmin,
+                                  const float4* prims, Hit64& h) {
+  const double* s = q + 16 * i;
+  V3d n(s[0], s[1], s[2]);
+  double denom = dot(n, d);
+  if (fabs(denom) < 1e-8) return;
+  double t = (s[3] - dot(n, o)) / denom;
+  if (!(t >= tmin && t <= h.t)) return;
+  V3d p = o + t * d;
+  V3d hp = p - V3d(s[4], s[5], s[6]);
+  V3d u(s[7], s[8], s[9]), v(s[10], s[11], s[12]), w(s[13], s[14], s[15]);
+  double alpha = dot(w, cross(hp, v));
+  double beta = dot(w, cross(u, hp));
+  if (!(alpha >= 0.0 && alpha <= 1.0 && beta >= 0.0 && beta <= 1.0)) return;
+  if (t == h.t && !tie_accept(prims, i | PRIM_QUAD_BIT, h.prim)) return;
+  h.t = t; h.prim = i | PRIM_QUAD_BIT;
+}
+
+__device__ inline void leaf_hit64(const DevScene& S, int leaf, V3d o, V3d d, double tmin, Hit64& h) {
+  int first = leaf >> 8, ns = (leaf >> 4) & 15, nq = leaf & 15;
+  for (int k = 0; k < ns; ++k) sphere_hit64(S.prims64, first + k, o, d, tmin, S.prims, h);
+  first += ns;
+  for (int k = 0; k < nq; ++k) quad_hit64(S.prims64, first + k, o, d, tmin, S.prims, h);
+}
+
+__device__ inline void world_hit64(const DevScene& S, V3d o, V3d d, double tmin, Hit64& h) {
+  int cur = S.root_ref;
+  if (cur < 0) { leaf_hit64(S, ~cur, o, d, tmin, h); return; }
+  const double idx = 1.0 / d.x, idy = 1.0 / d.y, idz = 1.0 / d.z;
+  int stack[RRT_STACK];
+  int sp = 0;
+  for (;;) {
+    if (cur >= 0) {
+      const float4* g = S.nodes + 4 * cur;
+      float4 n0 = ldg4(g), n1 = ldg4(g + 1), n2 = ldg4(g + 2), n3 = ldg4(g + 3);
+      double c0x0 = ((double)n0.x - o.x) * idx, c0x1 = ((double)n0.y - o.x) * idx;
+      double c0y0 = ((double)n0.z - o.y) * idy, c0y1 = ((double)n0.w - o.y) * idy;
+      double c0z0 = ((double)n2.x - o.z) * idz, c0z1 = ((double)n2.y - o.z) * idz;
+      double c1x0 = ((double)n1.x - o.x) * idx, c1x1 = ((double)n1.y - o.x) * idx;
+      double c1y0 = ((double)n1.z - o.y) * idy, c1y1 = ((double)n1.w - o.y) * idy;
+      double c1z0 = ((double)n2.z - o.z) * idz, c1z1 = ((double)n2.w - o.z) * idz;
+      double near0 = fmax(fmax(fmin(c0x0, c0x1), fmin(c0y0, c0y1)), fmax(fmin(c0z0, c0z1), tmin));
+      double far0 = fmin(fmin(fmax(c0x0, c0x1), fmax(c0y0, c0y1)), fmin(fmax(c0z0, c0z1), h.t));
+      double near1 = fmax(fmax(fmin(c1x0, c1x1), fmin(c1y0, c1y1)), fmax(fmin(c1z0, c1z1), tmin));
+      double far1 = fmin(fmin(fmax(c1x0, c1x1), fmax(c1y0, c1y1)), fmin(fmax(c1z0, c1z1), h.t));
+      bool hit0 = near0 <= far0, hit1 = near1 <= far1;
+      int r0 = __float_as_int(n3.x), r1 = __float_as_int(n3.y);
+      if (hit0 && hit1) {
+        if (near1 < near0) { int t = r0; r0 = r1; r1 = t; }
+        if (sp < RRT_STACK) stack[sp++] = r1;
+        cur = r0;
+        continue;
+      }
+      if (hit0) { cur = r0; continue; }
+      if (hit1) { cur = r1; continue; }
+    } else {
+      leaf_hit64(S, ~cur, o, d, tmin, h);
+    }
+    if (sp == 0) break;
+    cur = stack[--sp];
+  }
+}
+
+}  // namespace rrt

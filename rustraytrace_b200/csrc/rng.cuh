@@ -1,0 +1,46 @@
+// rng.cuh — counter-based Philox4x32-10 (Salmon et al., SC'11), keyed on the render seed and
+// counted by (pixel, sample, bounce, draw block).  Replaces the reference's thread-local
+// SmallRng::from_entropy() (the_rest_of_your_life/rtweekend.rs:9-25): only the distribution of
+// random_double() — uniform in [0,1) — is specified there, so any partition of the frame over
+// blocks, launches or GPUs sees the same numbers for the same (pixel, sample, bounce).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rrt {
+
+struct Rand4 { float x, y, z, w; };
+
+__host__ __device__ inline void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                             uint32_t k0, uint32_t k1, uint32_t out[4]) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+#if defined(__CUDA_ARCH__)
+    uint32_t hi0 = __umulhi(M0, c0), hi1 = __umulhi(M1, c2);
+#else
+    uint32_t hi0 = (uint32_t)(((uint64_t)M0 * c0) >> 32), hi1 = (uint32_t)(((uint64_t)M1 * c2) >> 32);
+#endif
+    uint32_t lo0 = M0 * c0, lo1 = M1 * c2;
+    uint32_t n0 = hi1 ^ c1 ^ k0;
+    uint32_t n2 = hi0 ^ c3 ^ k1;
+    c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+    k0 += W0; k1 += W1;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+// 24-bit mantissa fill: uniform in [0,1), never 1.0
+__host__ __device__ inline float u01(uint32_t x) { return (float)(x >> 8) * (1.0f / 16777216.0f); }
+
+struct PathRng {
+  uint32_t pixel, sample, k0, k1;
+  __device__ inline Rand4 draw(uint32_t bounce, uint32_t block) const {
+    uint32_t o[4];
+    philox4x32_10(pixel, sample, bounce, block, k0, k1, o);
+    Rand4 r; r.x = u01(o[0]); r.y = u01(o[1]); r.z = u01(o[2]); r.w = u01(o[3]);
+    return r;
+  }
+};
+
+}  // namespace rrt
