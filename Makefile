@@ -1,0 +1,42 @@
+# Builds everything in-tree (the .so files travel to the GPU box with the snapshot).
+#   librrt.so       CUDA kernels + C ABI (include/rrt.h), sm_100a only
+#   librrt_host.so  host mirror of the reference's Rust surface (include/rrt_host.h)
+#   bin/rrt         CLI mirroring src/main.rs
+#   oracle          CPU restatement (test infrastructure) -> oracle/liboracle.so
+NVCC      ?= nvcc
+CXX       ?= g++
+PKG       := rustraytrace_b200
+NVFLAGS   := -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 --use_fast_math \
+             -Xcompiler -fPIC -Xcompiler -Wall
+CXXFLAGS  := -O2 -std=c++17 -fPIC -Wall
+
+CSRC := $(PKG)/csrc
+HOST := $(PKG)/host
+
+all: $(PKG)/librrt.so $(PKG)/librrt_host.so $(PKG)/bin/rrt oracle
+
+$(CSRC)/kernels.o: $(CSRC)/kernels.cu $(CSRC)/*.cuh $(CSRC)/*.h include/rrt.h
+	$(NVCC) $(NVFLAGS) -c $< -o $@
+$(CSRC)/api.o: $(CSRC)/api.cu $(CSRC)/*.cuh $(CSRC)/*.h $(CSRC)/flatten.hpp include/rrt.h
+	$(NVCC) $(NVFLAGS) -c $< -o $@
+$(CSRC)/flatten.o: $(CSRC)/flatten.cpp $(CSRC)/flatten.hpp $(CSRC)/device_types.h include/rrt.h
+	$(NVCC) $(NVFLAGS) -x cu -c $< -o $@
+
+$(PKG)/librrt.so: $(CSRC)/kernels.o $(CSRC)/api.o $(CSRC)/flatten.o
+	$(NVCC) -shared -o $@ $^ -cudart shared
+
+$(PKG)/librrt_host.so: $(HOST)/books.cpp $(HOST)/rtw_image.cpp $(HOST)/render_io.cpp $(HOST)/*.hpp include/*.h
+	$(CXX) $(CXXFLAGS) -shared -o $@ $(HOST)/books.cpp $(HOST)/rtw_image.cpp $(HOST)/render_io.cpp
+
+$(PKG)/bin/rrt: $(HOST)/main.cpp $(PKG)/librrt.so $(PKG)/librrt_host.so
+	mkdir -p $(PKG)/bin
+	$(CXX) $(CXXFLAGS) -o $@ $(HOST)/main.cpp -L$(PKG) -lrrt -lrrt_host -Wl,-rpath,'$$ORIGIN/..'
+
+oracle:
+	$(MAKE) -C oracle
+
+clean:
+	rm -f $(CSRC)/*.o $(PKG)/*.so $(PKG)/bin/rrt
+	$(MAKE) -C oracle clean
+
+.PHONY: all oracle clean

@@ -216,6 +216,15 @@ int rrt_resolve_rgb8(rrt_ctx* ctx, const float* accum_host, int width, int heigh
                      uint8_t* rgb_host);
 
 int rrt_get_stats(const rrt_ctx* ctx, rrt_stats* out);
+
+/* Host-only hooks (no GPU needed; used by the CPU test tier):
+ *   rrt_flatten_check: runs the flattener + BVH build on the host and verifies the result (every
+ *   primitive in exactly one leaf, every child box inside its parent's).  Outputs may be NULL.
+ *   rrt_philox_kat:    one Philox4x32-10 block (the sampling RNG), for known-answer tests. */
+int rrt_flatten_check(const rrt_scene_desc* desc, int32_t* n_prims, int32_t* n_nodes, int32_t* bvh_depth,
+                      int32_t* n_media, int32_t* n_lights);
+void rrt_philox_kat(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1,
+                    uint32_t* out4);
 const char* rrt_last_error(void);
 const char* rrt_version(void);
 

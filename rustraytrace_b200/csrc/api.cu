@@ -1,0 +1,433 @@
+// api.cu — the extern "C" surface of librrt.so (include/rrt.h).  Host orchestration only: the
+// per-call flow mirrors cuda::imp::render (src/cuda/mod.rs:342-441) — device init, scene upload,
+// one kernel over the frame, read-back — minus the NVRTC step (kernels are compiled ahead of time
+// for sm_100a) and minus the per-pass relaunch/synchronise loop (:403-432): one persistent launch
+// covers every sample.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/rrt.h"
+#include "device_types.h"
+#include "flatten.hpp"
+#include "kernels.h"
+#include "rng.cuh"
+
+using namespace rrt;
+
+static thread_local std::string g_err;
+static int fail(int st, const std::string& m) { g_err = m; return st; }
+#define CK(call, what)                                                                   \
+  do {                                                                                   \
+    cudaError_t e_ = (call);                                                             \
+    if (e_ != cudaSuccess) return fail(RRT_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e_)); \
+  } while (0)
+
+struct rrt_ctx {
+  int device = 0;
+  int sm_count = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  unsigned int* counter = nullptr;
+  float* accum = nullptr;  // grow-only frame buffer for the host-output entry points
+  size_t accum_floats = 0;
+  rrt_stats stats;
+};
+
+struct rrt_scene {
+  rrt_ctx* ctx = nullptr;
+  std::vector<void*> allocs;
+  DevScene dev;
+  int n_nodes = 0, n_prims = 0, n_media = 0, n_lights = 0;
+  uint64_t h2d_bytes = 0;
+};
+
+template <typename T>
+static int upload(rrt_scene* sc, const std::vector<T>& v, const T** out) {
+  *out = nullptr;
+  if (v.empty()) return RRT_OK;
+  void* d = nullptr;
+  size_t bytes = v.size() * sizeof(T);
+  CK(cudaMalloc(&d, bytes), "cudaMalloc(scene)");
+  sc->allocs.push_back(d);
+  CK(cudaMemcpyAsync(d, v.data(), bytes, cudaMemcpyHostToDevice, sc->ctx->stream), "scene upload");
+  sc->h2d_bytes += bytes;
+  *out = reinterpret_cast<const T*>(d);
+  return RRT_OK;
+}
+
+extern "C" {
+
+const char* rrt_last_error(void) { return g_err.c_str(); }
+const char* rrt_version(void) { return "rrt-b200 0.1 (sm_100a)"; }
+
+int rrt_init(int device, rrt_ctx** out) {
+  if (!out) return fail(RRT_ERR_INVALID, "rrt_init: out is null");
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    cudaGetLastError();
+    return fail(RRT_ERR_NO_DEVICE, std::string("cuda init failed: no CUDA device (") +
+                                       (e != cudaSuccess ? cudaGetErrorString(e) : "count 0") +
+                                       "); this library has no CPU fallback");
+  }
+  if (device < 0 || device >= n) return fail(RRT_ERR_INVALID, "rrt_init: device index out of range");
+  CK(cudaSetDevice(device), "cuda init failed");
+  rrt_ctx* c = new rrt_ctx();
+  std::memset(&c->stats, 0, sizeof c->stats);
+  c->device = device;
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties");
+  if (prop.major < 10) {
+    delete c;
+    return fail(RRT_ERR_NO_DEVICE, std::string("device '") + prop.name + "' is not sm_100-class; kernels are built for sm_100a only");
+  }
+  c->sm_count = prop.multiProcessorCount;
+  CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "cudaStreamCreate");
+  for (auto& ev : c->ev) CK(cudaEventCreate(&ev), "cudaEventCreate");
+  CK(cudaMalloc(&c->counter, sizeof(unsigned int)), "cudaMalloc(counter)");
+  c->stats.sm_count = c->sm_count;
+  *out = c;
+  return RRT_OK;
+}
+
+void rrt_shutdown(rrt_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  if (c->accum) cudaFree(c->accum);
+  if (c->counter) cudaFree(c->counter);
+  for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+void rrt_scene_destroy(rrt_scene* sc) {
+  if (!sc) return;
+  cudaSetDevice(sc->ctx->device);
+  cudaStreamSynchronize(sc->ctx->stream);
+  for (void* p : sc->allocs) cudaFree(p);
+  delete sc;
+}
+
+int rrt_scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out) {
+  if (!c || !out) return fail(RRT_ERR_INVALID, "rrt_scene_create: null argument");
+  *out = nullptr;
+  FlatScene F;
+  std::string err;
+  int st = flatten_scene(desc, F, err);
+  if (st != RRT_OK) return fail(st, "scene flatten failed: " + err);
+  CK(cudaSetDevice(c->device), "cudaSetDevice");
+  rrt_scene* sc = new rrt_scene();
+  sc->ctx = c;
+  std::memset(&sc->dev, 0, sizeof sc->dev);
+  DevScene& D = sc->dev;
+  const unsigned char* texels = nullptr;
+  int rc = RRT_OK;
+  if ((rc = upload(sc, F.prims, &D.prims)) || (rc = upload(sc, F.prims64, &D.prims64)) ||
+      (rc = upload(sc, F.nodes, &D.nodes)) || (rc = upload(sc, F.bprims, &D.bprims)) ||
+      (rc = upload(sc, F.materials, &D.materials)) || (rc = upload(sc, F.textures, &D.textures)) ||
+      (rc = upload(sc, F.images, &D.images)) || (rc = upload(sc, F.texels, &texels)) ||
+      (rc = upload(sc, F.perlins, &D.perlins)) || (rc = upload(sc, F.media, &D.media)) ||
+      (rc = upload(sc, F.lights, &D.lights))) {
+    rrt_scene_destroy(sc);
+    return rc;
+  }
+  D.texels = texels;
+  D.root_ref = F.root_ref;
+  D.n_nodes = (int)(F.nodes.size() / 4);
+  D.n_prims = F.n_prims;
+  D.n_media = (int)F.media.size();
+  D.n_lights = (int)F.lights.size();
+  D.has_motion = F.has_motion;
+  D.smem_nodes = 0;
+  D.smem_prims = 0;
+  if (D.n_media > 5) { rrt_scene_destroy(sc); return fail(RRT_ERR_UNSUPPORTED, "more than 5 constant media"); }
+  sc->n_nodes = D.n_nodes; sc->n_prims = D.n_prims; sc->n_media = D.n_media; sc->n_lights = D.n_lights;
+  cudaError_t e = cudaStreamSynchronize(c->stream);  // host vectors die at return
+  if (e != cudaSuccess) { rrt_scene_destroy(sc); return fail(RRT_ERR_CUDA, std::string("scene upload: ") + cudaGetErrorString(e)); }
+  c->stats.h2d_bytes = sc->h2d_bytes;
+  c->stats.n_prims = sc->n_prims; c->stats.n_bvh_nodes = sc->n_nodes;
+  c->stats.n_media = sc->n_media; c->stats.n_lights = sc->n_lights;
+  *out = sc;
+  return RRT_OK;
+}
+
+int rrt_image_height(const rrt_camera* cam) {
+  if (!cam || !(cam->aspect_ratio > 0.0)) return 0;
+  int h = (int)((double)cam->image_width / cam->aspect_ratio);
+  return h < 1 ? 1 : h;
+}
+
+static int check_camera(const rrt_camera* cam, const rrt_render_params* p) {
+  if (!cam) return fail(RRT_ERR_INVALID, "camera is null");
+  if (cam->image_width < 1 || cam->image_width > 65536 || !(cam->aspect_ratio > 0.0))
+    return fail(RRT_ERR_INVALID, "camera: image_width/aspect_ratio out of range");
+  if (p) {
+    if (p->integrator < RRT_INT_BOOK1 || p->integrator > RRT_INT_BOOK3) return fail(RRT_ERR_INVALID, "params: unknown integrator");
+    if (p->shard_mode < RRT_SHARD_NONE || p->shard_mode > RRT_SHARD_SAMPLE) return fail(RRT_ERR_INVALID, "params: unknown shard mode");
+    if (p->shard_mode != RRT_SHARD_NONE && (p->world < 1 || p->rank < 0 || p->rank >= p->world))
+      return fail(RRT_ERR_INVALID, "params: rank/world out of range");
+    if (cam->samples_per_pixel < 0 || cam->max_depth < 0) return fail(RRT_ERR_INVALID, "camera: negative spp or depth");
+  }
+  return RRT_OK;
+}
+
+int rrt_render_device(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, const rrt_render_params* p,
+                      float* accum_dev) {
+  if (!c || !sc || !p || !accum_dev) return fail(RRT_ERR_INVALID, "rrt_render_device: null argument");
+  if (sc->ctx != c) return fail(RRT_ERR_INVALID, "scene belongs to another context");
+  int rc = check_camera(cam, p);
+  if (rc) return rc;
+  CK(cudaSetDevice(c->device), "cudaSetDevice");
+  RenderArgs A;
+  std::memset(&A, 0, sizeof A);
+  A.S = sc->dev;
+  DevCamera64 c64;
+  const int H = camera_initialize(cam, A.cam, c64);
+  const int Wd = cam->image_width;
+  DevWork& W = A.W;
+  W.width = Wd; W.height = H;
+  W.integrator = p->integrator;
+  W.max_depth = cam->max_depth;
+  W.shard_mode = p->shard_mode;
+  W.rank = p->shard_mode == RRT_SHARD_NONE ? 0 : p->rank;
+  W.world = p->shard_mode == RRT_SHARD_NONE ? 1 : p->world;
+  W.seed_lo = (unsigned)(p->seed & 0xffffffffu); W.seed_hi = (unsigned)(p->seed >> 32);
+  int spp_eff = cam->samples_per_pixel;
+  if (p->integrator == RRT_INT_BOOK3) spp_eff = A.cam.sqrt_spp * A.cam.sqrt_spp;  // camera.rs:114-116
+  W.spp_eff = spp_eff;
+  W.s_begin = 0; W.s_end = spp_eff;
+  if (p->shard_mode == RRT_SHARD_SAMPLE) {
+    W.s_begin = (int)(((long long)spp_eff * W.rank) / W.world);
+    W.s_end = (int)(((long long)spp_eff * (W.rank + 1)) / W.world);
+  }
+  W.stiles_x = (Wd + 31) / 32; W.stiles_y = (H + 31) / 32;
+  const int n_super = W.stiles_x * W.stiles_y;
+  const int tw = p->shard_mode == RRT_SHARD_TILE ? W.world : 1, tr = p->shard_mode == RRT_SHARD_TILE ? W.rank : 0;
+  const int my_super = tr < n_super ? (n_super - tr + tw - 1) / tw : 0;
+  W.n_tiles = my_super * 32;
+  W.tiles_x = W.stiles_x * 4;
+  // pixels owned by this rank
+  double my_pixels = 0;
+  for (int k = tr; k < n_super; k += tw) {
+    int sx = k % W.stiles_x, sy = k / W.stiles_x;
+    my_pixels += (double)std::min(32, Wd - sx * 32) * (double)std::min(32, H - sy * 32);
+  }
+  const int n_samples = W.s_end - W.s_begin;
+
+  // shared-memory prefix of the BVH and grid size
+  A.S.smem_nodes = std::min(A.S.n_nodes, 640);
+  size_t smem = (size_t)A.S.smem_nodes * 64;
+  int bps = render_blocks_per_sm(p->integrator, smem);
+  if (bps < 1) return fail(RRT_ERR_CUDA, "kernel launch failed: render kernel does not fit on an SM");
+  const int grid = c->sm_count * bps;
+  const long long resident_warps = (long long)grid * (RRT_BLOCK / 32);
+  long long chunks = 1;
+  if (W.n_tiles > 0 && n_samples > 0) {
+    long long want = (48 * resident_warps + W.n_tiles - 1) / W.n_tiles;
+    long long cap = std::max(1, n_samples / 16);
+    chunks = std::max(1LL, std::min(want, cap));
+  }
+  W.chunks = (int)chunks;
+  W.atomic_accum = chunks > 1 ? 1 : 0;
+  A.accum = reinterpret_cast<float4*>(accum_dev);
+  A.counter = c->counter;
+
+  CK(cudaEventRecord(c->ev[0], c->stream), "cudaEventRecord");
+  CK(cudaMemsetAsync(c->counter, 0, sizeof(unsigned int), c->stream), "cudaMemsetAsync(counter)");
+  if (W.atomic_accum || p->shard_mode == RRT_SHARD_TILE || n_samples <= 0)
+    CK(cudaMemsetAsync(accum_dev, 0, (size_t)Wd * H * 4 * sizeof(float), c->stream), "cudaMemsetAsync(accum)");
+  int launches = 0;
+  CK(cudaEventRecord(c->ev[1], c->stream), "cudaEventRecord");
+  if (W.n_tiles > 0 && n_samples > 0) {
+    CK(launch_render(A, grid, smem, c->stream), "kernel launch failed");
+    launches = 1;
+  }
+  CK(cudaEventRecord(c->ev[2], c->stream), "cudaEventRecord");
+  CK(cudaStreamSynchronize(c->stream), "render kernel failed");
+  float kms = 0, tms = 0;
+  cudaEventElapsedTime(&kms, c->ev[1], c->ev[2]);
+  cudaEventElapsedTime(&tms, c->ev[0], c->ev[2]);
+  rrt_stats& st = c->stats;
+  st.width = Wd; st.height = H; st.spp_effective = spp_eff;
+  st.kernel_launches = launches;
+  st.paths = my_pixels * (double)std::max(0, n_samples);
+  st.kernel_ms = kms; st.total_ms = tms;
+  st.d2h_bytes = 0;
+  st.n_prims = sc->n_prims; st.n_bvh_nodes = sc->n_nodes; st.n_media = sc->n_media; st.n_lights = sc->n_lights;
+  st.sm_count = c->sm_count;
+  return RRT_OK;
+}
+
+static int ensure_accum(rrt_ctx* c, size_t floats) {
+  if (c->accum_floats >= floats) return RRT_OK;
+  if (c->accum) { cudaFree(c->accum); c->accum = nullptr; c->accum_floats = 0; }
+  CK(cudaMalloc(&c->accum, floats * sizeof(float)), "cudaMalloc(accum)");
+  c->accum_floats = floats;
+  return RRT_OK;
+}
+
+int rrt_render(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, const rrt_render_params* p, float* accum_host) {
+  if (!c || !accum_host) return fail(RRT_ERR_INVALID, "rrt_render: null argument");
+  int rc = check_camera(cam, p);
+  if (rc) return rc;
+  CK(cudaSetDevice(c->device), "cudaSetDevice");
+  const int H = rrt_image_height(cam);
+  const size_t floats = (size_t)cam->image_width * H * 4;
+  if ((rc = ensure_accum(c, floats))) return rc;
+  if ((rc = rrt_render_device(c, sc, cam, p, c->accum))) return rc;
+  CK(cudaMemcpyAsync(accum_host, c->accum, floats * sizeof(float), cudaMemcpyDeviceToHost, c->stream), "accum read-back");
+  CK(cudaEventRecord(c->ev[3], c->stream), "cudaEventRecord");
+  CK(cudaStreamSynchronize(c->stream), "accum read-back");
+  float tms = 0;
+  cudaEventElapsedTime(&tms, c->ev[0], c->ev[3]);
+  c->stats.total_ms = tms;
+  c->stats.d2h_bytes = floats * sizeof(float);
+  return RRT_OK;
+}
+
+int rrt_render_frame(rrt_ctx* c, const rrt_scene_desc* desc, const rrt_camera* cam, const rrt_render_params* p,
+                     float* accum_host) {
+  rrt_scene* sc = nullptr;
+  int rc = rrt_scene_create(c, desc, &sc);
+  if (rc) return rc;
+  rc = rrt_render(c, sc, cam, p, accum_host);
+  uint64_t h2d = sc->h2d_bytes;
+  rrt_scene_destroy(sc);
+  if (rc == RRT_OK) c->stats.h2d_bytes = h2d;
+  return rc;
+}
+
+int rrt_probe(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, int precision, int32_t* prim_id, double* t) {
+  if (!c || !sc || !prim_id || !t) return fail(RRT_ERR_INVALID, "rrt_probe: null argument");
+  if (precision != 32 && precision != 64) return fail(RRT_ERR_INVALID, "rrt_probe: precision must be 32 or 64");
+  int rc = check_camera(cam, nullptr);
+  if (rc) return rc;
+  CK(cudaSetDevice(c->device), "cudaSetDevice");
+  ProbeArgs A;
+  std::memset(&A, 0, sizeof A);
+  A.S = sc->dev;
+  A.S.smem_nodes = 0;
+  A.height = camera_initialize(cam, A.cam, A.cam64);
+  A.width = cam->image_width;
+  size_t n = (size_t)A.width * A.height;
+  CK(cudaMalloc(&A.prim_id, n * sizeof(int)), "cudaMalloc(probe)");
+  cudaError_t e = cudaMalloc(&A.t, n * sizeof(double));
+  if (e != cudaSuccess) { cudaFree(A.prim_id); return fail(RRT_ERR_CUDA, std::string("cudaMalloc(probe): ") + cudaGetErrorString(e)); }
+  e = launch_probe(A, precision, c->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(prim_id, A.prim_id, n * sizeof(int), cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(t, A.t, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+  cudaFree(A.prim_id); cudaFree(A.t);
+  if (e != cudaSuccess) return fail(RRT_ERR_CUDA, std::string("probe kernel failed: ") + cudaGetErrorString(e));
+  c->stats.kernel_launches = 1;
+  c->stats.width = A.width; c->stats.height = A.height;
+  return RRT_OK;
+}
+
+int rrt_resolve_rgb8_device(rrt_ctx* c, const float* accum_dev, int width, int height, int spp, uint8_t* rgb_dev) {
+  if (!c || !accum_dev || !rgb_dev || width < 1 || height < 1) return fail(RRT_ERR_INVALID, "rrt_resolve_rgb8_device: bad argument");
+  CK(cudaSetDevice(c->device), "cudaSetDevice");
+  CK(launch_resolve(accum_dev, width * height, spp, rgb_dev, c->stream), "kernel launch failed");
+  CK(cudaStreamSynchronize(c->stream), "resolve kernel failed");
+  c->stats.kernel_launches = 1;
+  return RRT_OK;
+}
+
+int rrt_resolve_rgb8(rrt_ctx* c, const float* accum_host, int width, int height, int spp, uint8_t* rgb_host) {
+  if (!c || !accum_host || !rgb_host || width < 1 || height < 1) return fail(RRT_ERR_INVALID, "rrt_resolve_rgb8: bad argument");
+  CK(cudaSetDevice(c->device), "cudaSetDevice");
+  size_t n = (size_t)width * height;
+  int rc = ensure_accum(c, n * 4);
+  if (rc) return rc;
+  unsigned char* rgb = nullptr;
+  CK(cudaMalloc(&rgb, n * 3), "cudaMalloc(rgb)");
+  cudaError_t e = cudaMemcpyAsync(c->accum, accum_host, n * 16, cudaMemcpyHostToDevice, c->stream);
+  if (e == cudaSuccess) e = launch_resolve(c->accum, (int)n, spp, rgb, c->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(rgb_host, rgb, n * 3, cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+  cudaFree(rgb);
+  if (e != cudaSuccess) return fail(RRT_ERR_CUDA, std::string("resolve failed: ") + cudaGetErrorString(e));
+  c->stats.kernel_launches = 1;
+  return RRT_OK;
+}
+
+int rrt_get_stats(const rrt_ctx* c, rrt_stats* out) {
+  if (!c || !out) return fail(RRT_ERR_INVALID, "rrt_get_stats: null argument");
+  *out = c->stats;
+  return RRT_OK;
+}
+
+// Known-answer hook for the sampling RNG (tests): Philox4x32-10 block.
+void rrt_philox_kat(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t* out4) {
+  philox4x32_10(c0, c1, c2, c3, k0, k1, out4);
+}
+
+}  // extern "C"
+
+// ---- host-only verification of the flattener (CPU test tier) --------------------------------
+namespace {
+struct Box { float lo[3], hi[3]; };
+bool inside(const Box& c, const Box& p) {
+  for (int a = 0; a < 3; ++a) if (c.lo[a] < p.lo[a] || c.hi[a] > p.hi[a]) return false;
+  return true;
+}
+int as_int(float f) { int i; std::memcpy(&i, &f, 4); return i; }
+}  // namespace
+
+extern "C" int rrt_flatten_check(const rrt_scene_desc* desc, int32_t* n_prims, int32_t* n_nodes, int32_t* bvh_depth,
+                                 int32_t* n_media, int32_t* n_lights) {
+  FlatScene F;
+  std::string err;
+  int st = flatten_scene(desc, F, err);
+  if (st != RRT_OK) return fail(st, "scene flatten failed: " + err);
+  const int nn = (int)(F.nodes.size() / 4);
+  std::vector<int> seen(F.n_prims, 0);
+  std::vector<int> node_seen(nn, 0);
+  auto mark_leaf = [&](int ref) -> bool {
+    int leaf = ~ref, first = leaf >> 8, ns = (leaf >> 4) & 15, nq = leaf & 15;
+    if (first < 0 || first + ns + nq > F.n_prims) return false;
+    for (int k = first; k < first + ns + nq; ++k) seen[k]++;
+    return true;
+  };
+  if (F.root_ref < 0) {
+    if (!mark_leaf(F.root_ref)) return fail(RRT_ERR_INVALID, "flatten check: root leaf out of range");
+  } else {
+    struct Item { int node; Box box; bool has_box; };
+    std::vector<Item> stack;
+    Item root; root.node = 0; root.has_box = false;
+    stack.push_back(root);
+    while (!stack.empty()) {
+      Item it = stack.back(); stack.pop_back();
+      if (it.node < 0 || it.node >= nn) return fail(RRT_ERR_INVALID, "flatten check: node index out of range");
+      if (node_seen[it.node]++) return fail(RRT_ERR_INVALID, "flatten check: node reached twice");
+      const float4* n = &F.nodes[4 * it.node];
+      Box c0 = {{n[0].x, n[0].z, n[2].x}, {n[0].y, n[0].w, n[2].y}};
+      Box c1 = {{n[1].x, n[1].z, n[2].z}, {n[1].y, n[1].w, n[2].w}};
+      if (it.has_box && (!inside(c0, it.box) || !inside(c1, it.box)))
+        return fail(RRT_ERR_INVALID, "flatten check: child box escapes its parent");
+      int refs[2] = {as_int(n[3].x), as_int(n[3].y)};
+      Box bx[2] = {c0, c1};
+      for (int k = 0; k < 2; ++k) {
+        if (refs[k] >= 0) { Item ch; ch.node = refs[k]; ch.box = bx[k]; ch.has_box = true; stack.push_back(ch); }
+        else if (!mark_leaf(refs[k])) return fail(RRT_ERR_INVALID, "flatten check: leaf out of range");
+      }
+    }
+    for (int i = 0; i < nn; ++i) if (node_seen[i] != 1) return fail(RRT_ERR_INVALID, "flatten check: unreachable node");
+  }
+  for (int i = 0; i < F.n_prims; ++i)
+    if (seen[i] != 1) return fail(RRT_ERR_INVALID, "flatten check: primitive not in exactly one leaf");
+  if (n_prims) *n_prims = F.n_prims;
+  if (n_nodes) *n_nodes = nn;
+  if (bvh_depth) *bvh_depth = F.bvh_depth;
+  if (n_media) *n_media = (int)F.media.size();
+  if (n_lights) *n_lights = (int)F.lights.size();
+  return RRT_OK;
+}

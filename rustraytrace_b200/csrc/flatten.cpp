@@ -309,6 +309,14 @@ void box32(const double* lo, const double* hi, float* flo, float* fhi) {
   }
 }
 
+bool tex_reads_uv(const rrt_scene_desc* d, int t, int depth) {  // only ImageTexture reads (u,v)
+  if (t < 0 || t >= d->n_textures || depth > 8) return false;
+  const rrt_texture& x = d->textures[t];
+  if (x.kind == RRT_T_IMAGE) return true;
+  if (x.kind == RRT_T_CHECKER) return tex_reads_uv(d, x.even, depth + 1) || tex_reads_uv(d, x.odd, depth + 1);
+  return false;
+}
+
 bool tex_needs_ok(const rrt_scene_desc* d, int t, int depth) {
   if (t < 0) return true;
   if (t >= d->n_textures || depth > 8) return false;
@@ -351,6 +359,7 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
       dm.albedo = f4(t.color[0], t.color[1], t.color[2], 0);
       dm.tex = -1;
     }
+    dm.albedo.w = (dm.tex >= 0 && tex_reads_uv(desc, dm.tex, 0)) ? 1.0f : 0.0f;  // needs sphere uv
     out.materials.push_back(dm);
   }
   for (int i = 0; i < desc->n_textures; ++i) {
