@@ -13,16 +13,18 @@ CXXFLAGS  := -O2 -std=c++17 -fPIC -Wall
 CSRC := $(PKG)/csrc
 HOST := $(PKG)/host
 
-all: $(PKG)/librrt.so $(PKG)/librrt_host.so $(PKG)/bin/rrt oracle
+all: $(PKG)/librrt.so $(PKG)/librrt_host.so oracle
 
 $(CSRC)/kernels.o: $(CSRC)/kernels.cu $(CSRC)/*.cuh $(CSRC)/*.h include/rrt.h
 	$(NVCC) $(NVFLAGS) -c $< -o $@
+$(CSRC)/probe64.o: $(CSRC)/probe64.cu $(CSRC)/*.cuh $(CSRC)/*.h include/rrt.h
+	$(NVCC) -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -fmad=false -Xcompiler -fPIC -c $< -o $@
 $(CSRC)/api.o: $(CSRC)/api.cu $(CSRC)/*.cuh $(CSRC)/*.h $(CSRC)/flatten.hpp include/rrt.h
 	$(NVCC) $(NVFLAGS) -c $< -o $@
 $(CSRC)/flatten.o: $(CSRC)/flatten.cpp $(CSRC)/flatten.hpp $(CSRC)/device_types.h include/rrt.h
 	$(NVCC) $(NVFLAGS) -x cu -c $< -o $@
 
-$(PKG)/librrt.so: $(CSRC)/kernels.o $(CSRC)/api.o $(CSRC)/flatten.o
+$(PKG)/librrt.so: $(CSRC)/kernels.o $(CSRC)/probe64.o $(CSRC)/api.o $(CSRC)/flatten.o
 	$(NVCC) -shared -o $@ $^ -cudart shared
 
 $(PKG)/librrt_host.so: $(HOST)/books.cpp $(HOST)/rtw_image.cpp $(HOST)/render_io.cpp $(HOST)/*.hpp include/*.h

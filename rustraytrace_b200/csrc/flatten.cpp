@@ -89,8 +89,178 @@ void bake_quad(const rrt_hittable& h, int id, const Xform& X, BakedPrim& p) {
 
 struct BakedMedium { int first, count, mat, id; double density; };
 
+// ------------------------------------------------------------------------------------------------
+// Reference traversal order.  At an exact equal-t tie the reference's answer depends on the order
+// in which it visits primitives: list order (hittable_list.rs:46-51), and inside a BvhNode the
+// left-then-right order of the tree that BvhNode::build produced (bvh.rs:159-172).  To give every
+// primitive the same rank the reference would, the flattener replays the reference's bounding
+// boxes (aabb.rs, sphere.rs:19-41, quad.rs:50-54, hittable.rs:79-82, 107-139) and its 12-bucket
+// SAH partition (bvh.rs:21-156) — only to obtain the visiting order; the tree itself is discarded.
+struct RBox {
+  double lo[3], hi[3];
+  static RBox empty() {
+    RBox b;
+    for (int a = 0; a < 3; ++a) { b.lo[a] = std::numeric_limits<double>::infinity(); b.hi[a] = -b.lo[a]; }
+    return b;
+  }
+  void pad() {  // Aabb::new -> pad_to_minimums, aabb.rs:24-28, 107-118
+    const double delta = 0.0001;
+    for (int a = 0; a < 3; ++a)
+      if (hi[a] - lo[a] < delta) { double p = delta / 2.0; lo[a] -= p; hi[a] += p; }
+  }
+  static RBox from_points(D3 p, D3 q) {  // aabb.rs:30-35
+    RBox b;
+    for (int a = 0; a < 3; ++a) { if (p[a] <= q[a]) { b.lo[a] = p[a]; b.hi[a] = q[a]; } else { b.lo[a] = q[a]; b.hi[a] = p[a]; } }
+    b.pad();
+    return b;
+  }
+  static RBox from_boxes(const RBox& x, const RBox& y) {  // aabb.rs:37-43, interval.rs:19-24
+    RBox b;
+    for (int a = 0; a < 3; ++a) { b.lo[a] = x.lo[a] <= y.lo[a] ? x.lo[a] : y.lo[a]; b.hi[a] = x.hi[a] >= y.hi[a] ? x.hi[a] : y.hi[a]; }
+    b.pad();
+    return b;
+  }
+  int longest_axis() const {  // aabb.rs:86-98
+    double sx = hi[0] - lo[0], sy = hi[1] - lo[1], sz = hi[2] - lo[2];
+    if (sx > sy) return sx > sz ? 0 : 2;
+    return sy > sz ? 1 : 2;
+  }
+  double surface_area() const {  // aabb.rs:100-105
+    double a = hi[0] - lo[0], b = hi[1] - lo[1], c = hi[2] - lo[2];
+    return 2.0 * (a * b + a * c + b * c);
+  }
+};
+
+struct RefOrder {
+  const rrt_scene_desc* d;
+  std::vector<RBox> memo;
+  std::vector<char> have;
+  explicit RefOrder(const rrt_scene_desc* desc) : d(desc), memo(desc->n_hittables), have(desc->n_hittables, 0) {}
+
+  // Hittable::bounding_box of the reference object behind desc index idx (indices already validated)
+  RBox bbox(int idx, int depth = 0) {
+    if (idx < 0 || idx >= d->n_hittables || depth > 64) return RBox::empty();
+    if (have[idx]) return memo[idx];
+    const rrt_hittable& h = d->hittables[idx];
+    RBox b = RBox::empty();
+    switch (h.kind) {
+      case RRT_H_SPHERE: {
+        D3 c0(h.a), c1 = D3(h.a) + D3(h.b), rv(h.c[0], h.c[0], h.c[0]);
+        b = RBox::from_points(c0 - rv, c0 + rv);
+        if (h.b[0] != 0 || h.b[1] != 0 || h.b[2] != 0) b = RBox::from_boxes(b, RBox::from_points(c1 - rv, c1 + rv));
+        break;
+      }
+      case RRT_H_QUAD: {
+        D3 q(h.a), u(h.b), v(h.c);
+        b = RBox::from_boxes(RBox::from_points(q, q + u + v), RBox::from_points(q + u, q + v));
+        break;
+      }
+      case RRT_H_LIST:  // hittable_list.rs:25-33
+        for (int k = 0; k < h.n_children; ++k) {
+          RBox cb = bbox(d->children[h.first_child + k], depth + 1);
+          b = k == 0 ? cb : RBox::from_boxes(b, cb);
+        }
+        break;
+      case RRT_H_BVH:  // bvh.rs:24-27
+        for (int k = 0; k < h.n_children; ++k) b = RBox::from_boxes(b, bbox(d->children[h.first_child + k], depth + 1));
+        break;
+      case RRT_H_TRANSLATE: {  // hittable.rs:79-82, aabb.rs:121-127
+        RBox cb = bbox(h.first_child, depth + 1);
+        for (int a = 0; a < 3; ++a) { b.lo[a] = cb.lo[a] + h.a[a]; b.hi[a] = cb.hi[a] + h.a[a]; }
+        b.pad();
+        break;
+      }
+      case RRT_H_ROTATE_Y: {  // hittable.rs:107-139
+        RBox cb = bbox(h.first_child, depth + 1);
+        double radians = h.a[0] * M_PI / 180.0, st = std::sin(radians), ct = std::cos(radians);
+        double inf = std::numeric_limits<double>::infinity();
+        D3 mn(inf, inf, inf), mx(-inf, -inf, -inf);
+        for (int i = 0; i < 2; ++i) for (int j = 0; j < 2; ++j) for (int k = 0; k < 2; ++k) {
+          double x = i ? cb.hi[0] : cb.lo[0], y = j ? cb.hi[1] : cb.lo[1], z = k ? cb.hi[2] : cb.lo[2];
+          double t[3] = {ct * x + st * z, y, -st * x + ct * z};
+          mn = D3(std::fmin(mn.x, t[0]), std::fmin(mn.y, t[1]), std::fmin(mn.z, t[2]));
+          mx = D3(std::fmax(mx.x, t[0]), std::fmax(mx.y, t[1]), std::fmax(mx.z, t[2]));
+        }
+        b = RBox::from_points(mn, mx);
+        break;
+      }
+      case RRT_H_CONSTANT_MEDIUM: b = bbox(h.first_child, depth + 1); break;  // constant_medium.rs:81-83
+      default: break;
+    }
+    memo[idx] = b; have[idx] = 1;
+    return b;
+  }
+
+  // BvhNode::build (bvh.rs:21-156) on objs[first, first+span): appends the left-to-right visiting
+  // order of the resulting tree to `out`.
+  void build(std::vector<int>& objs, size_t first, size_t span, std::vector<int>& out) {
+    if (span == 0) return;
+    if (span == 1) { out.push_back(objs[first]); return; }  // left == right: same object twice, one rank
+    if (span == 2) { out.push_back(objs[first]); out.push_back(objs[first + 1]); return; }
+    RBox box = RBox::empty();
+    for (size_t i = 0; i < span; ++i) box = RBox::from_boxes(box, bbox(objs[first + i]));
+    const size_t NB = 12;
+    const int axis = box.longest_axis();
+    auto median = [&]() {
+      std::stable_sort(objs.begin() + first, objs.begin() + first + span,
+                       [&](int a, int b) { return bbox(a).lo[axis] < bbox(b).lo[axis]; });
+      size_t mid = span / 2;
+      build(objs, first, mid, out);
+      build(objs, first + mid, span - mid, out);
+    };
+    double cmin = std::numeric_limits<double>::infinity(), cmax = -cmin;
+    for (size_t i = 0; i < span; ++i) {
+      RBox b = bbox(objs[first + i]);
+      double c = 0.5 * (b.lo[axis] + b.hi[axis]);
+      if (c < cmin) cmin = c;
+      if (c > cmax) cmax = c;
+    }
+    if (std::fabs(cmax - cmin) < 1e-12) { median(); return; }
+    auto bucket_of = [&](int obj) {
+      RBox b = bbox(obj);
+      double c = 0.5 * (b.lo[axis] + b.hi[axis]);
+      double f = (c - cmin) / (cmax - cmin) * (double)NB;
+      size_t idx = f > 0.0 ? (size_t)f : 0;  // `as usize` saturates
+      if (idx >= NB) idx = NB - 1;
+      return idx;
+    };
+    size_t count[NB] = {0};
+    RBox bb[NB];
+    for (size_t k = 0; k < NB; ++k) bb[k] = RBox::empty();
+    for (size_t i = 0; i < span; ++i) {
+      size_t k = bucket_of(objs[first + i]);
+      count[k] += 1;
+      bb[k] = RBox::from_boxes(bb[k], bbox(objs[first + i]));
+    }
+    RBox rbox[NB];
+    size_t rcount[NB];
+    RBox acc = RBox::empty();
+    size_t accn = 0;
+    for (size_t k = NB; k-- > 0;) { accn += count[k]; acc = RBox::from_boxes(acc, bb[k]); rbox[k] = acc; rcount[k] = accn; }
+    RBox lbox = RBox::empty();
+    size_t lcount = 0, best_split = 0;
+    double best_cost = std::numeric_limits<double>::infinity();
+    for (size_t k = 0; k + 1 < NB; ++k) {
+      lcount += count[k];
+      lbox = RBox::from_boxes(lbox, bb[k]);
+      if (lcount == 0 || rcount[k + 1] == 0) continue;
+      double cost = lbox.surface_area() * (double)lcount + rbox[k + 1].surface_area() * (double)rcount[k + 1];
+      if (cost < best_cost) { best_cost = cost; best_split = k; }
+    }
+    if (!std::isfinite(best_cost)) { median(); return; }
+    size_t mid = 0;
+    for (size_t i = 0; i < span; ++i)
+      if (bucket_of(objs[first + i]) <= best_split) { std::swap(objs[first + i], objs[first + mid]); mid += 1; }
+    if (mid == 0 || mid == span) { median(); return; }
+    build(objs, first, mid, out);
+    build(objs, first + mid, span - mid, out);
+  }
+};
+
 struct Walker {
   const rrt_scene_desc* d;
+  RefOrder ref;
+  explicit Walker(const rrt_scene_desc* desc) : d(desc), ref(desc) {}
   std::vector<BakedPrim> world;
   std::vector<BakedPrim> boundary;
   std::vector<BakedMedium> media;
@@ -119,8 +289,16 @@ struct Walker {
       case RRT_H_LIST: case RRT_H_BVH: {
         if (h.first_child < 0 || h.n_children < 0 || h.first_child + h.n_children > d->n_children)
           return fail(RRT_ERR_INVALID, "list children range out of bounds");
-        for (int k = 0; k < h.n_children; ++k)
-          if (!walk(d->children[h.first_child + k], X, out, depth + 1, in_boundary)) return false;
+        std::vector<int> kids(d->children + h.first_child, d->children + h.first_child + h.n_children);
+        for (int k : kids)
+          if (k < 0 || k >= d->n_hittables) return fail(RRT_ERR_INVALID, "hittable index out of range");
+        if (h.kind == RRT_H_BVH && kids.size() > 2) {  // visit in the order BvhNode::hit would
+          std::vector<int> ordered;
+          ref.build(kids, 0, kids.size(), ordered);
+          kids.swap(ordered);
+        }
+        for (int k : kids)
+          if (!walk(k, X, out, depth + 1, in_boundary)) return false;
         return true;
       }
       case RRT_H_TRANSLATE: {  // hittable.rs:86-93: p_parent = p_child + offset
@@ -337,7 +515,7 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
       (desc->n_perlins > 0 && !desc->perlins)) {
     err = "scene description has a null array with a positive count"; return RRT_ERR_INVALID;
   }
-  Walker w; w.d = desc;
+  Walker w(desc);
   Xform I;
   if (desc->n_hittables > 0 || desc->world >= 0) {
     if (!w.walk(desc->world, I, w.world, 0, false)) { err = w.err; return w.status; }

@@ -29,6 +29,7 @@ struct ProbeArgs {
 cudaError_t launch_render(const RenderArgs& A, int grid, size_t smem, cudaStream_t st);
 int render_blocks_per_sm(int integrator, size_t smem);
 cudaError_t launch_probe(const ProbeArgs& A, int precision, cudaStream_t st);
+cudaError_t launch_probe64(const ProbeArgs& A, cudaStream_t st);  // probe64.cu (-fmad=false)
 cudaError_t launch_resolve(const float* accum, int n, int spp, unsigned char* rgb, cudaStream_t st);
 
 }  // namespace rrt
