@@ -177,6 +177,12 @@ typedef struct rrt_scene rrt_scene;
 int rrt_init(int device, rrt_ctx** out);
 void rrt_shutdown(rrt_ctx* ctx);
 
+/* Launch on the caller's CUDA stream (a cudaStream_t, e.g. torch.cuda.current_stream().cuda_stream)
+ * instead of the context's own; NULL restores the library's stream.  The reference has one implicit
+ * stream per CudaDevice (cudarc, src/cuda/mod.rs:343); this makes the same choice explicit so the
+ * render can be ordered with the caller's NCCL reduce and timed with the caller's events. */
+int rrt_set_stream(rrt_ctx* ctx, void* cuda_stream);
+
 /* htod of the scene, src/cuda/mod.rs:389-390 — plus instance baking and the BVH build that
  * replace BvhNode::new (bvh.rs:21-156). */
 int rrt_scene_create(rrt_ctx* ctx, const rrt_scene_desc* desc, rrt_scene** out);
@@ -216,6 +222,12 @@ int rrt_resolve_rgb8(rrt_ctx* ctx, const float* accum_host, int width, int heigh
                      uint8_t* rgb_host);
 
 int rrt_get_stats(const rrt_ctx* ctx, rrt_stats* out);
+
+/* Host-only: the share of the frame rrt_render gives to params->rank (what rayon's row split,
+ * camera.rs:70-72, and the CUDA path's pass loop, src/cuda/mod.rs:403-432, become across GPUs).
+ * Outputs may be NULL; owner_mask is W*H bytes, 1 where this rank writes the pixel. */
+int rrt_shard_plan(const rrt_camera* cam, const rrt_render_params* params, int32_t* sample_begin,
+                   int32_t* sample_end, int32_t* n_super_tiles, double* n_pixels, uint8_t* owner_mask);
 
 /* Host-only hooks (no GPU needed; used by the CPU test tier):
  *   rrt_flatten_check: runs the flattener + BVH build on the host and verifies the result (every

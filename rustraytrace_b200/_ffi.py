@@ -94,6 +94,7 @@ VP = C.c_void_p
 RRT_SYMBOLS = [
     ("rrt_init", c_int, [c_int, C.POINTER(VP)]),
     ("rrt_shutdown", None, [VP]),
+    ("rrt_set_stream", c_int, [VP, VP]),
     ("rrt_scene_create", c_int, [VP, C.POINTER(SceneDesc), C.POINTER(VP)]),
     ("rrt_scene_destroy", None, [VP]),
     ("rrt_image_height", c_int, [C.POINTER(Camera)]),
@@ -104,6 +105,8 @@ RRT_SYMBOLS = [
     ("rrt_resolve_rgb8_device", c_int, [VP, VP, c_int, c_int, c_int, VP]),
     ("rrt_resolve_rgb8", c_int, [VP, VP, c_int, c_int, c_int, VP]),
     ("rrt_get_stats", c_int, [VP, C.POINTER(Stats)]),
+    ("rrt_shard_plan", c_int, [C.POINTER(Camera), C.POINTER(RenderParams), C.POINTER(c_int), C.POINTER(c_int),
+                               C.POINTER(c_int), C.POINTER(c_dbl), VP]),
     ("rrt_flatten_check", c_int, [C.POINTER(SceneDesc)] + [C.POINTER(c_int)] * 5),
     ("rrt_philox_kat", None, [C.c_uint32] * 6 + [C.POINTER(C.c_uint32)]),
     ("rrt_last_error", C.c_char_p, []),

@@ -201,6 +201,22 @@ def flatten_check(desc):
     return dict(zip(("n_prims", "n_nodes", "bvh_depth", "n_media", "n_lights"), [x.value for x in v]))
 
 
+def shard_plan(camera, integrator, shard_mode, rank, world, mask=False):
+    """rrt_shard_plan (host only): this rank's sample range / tiles / pixel count [/ owner mask]."""
+    p = F.RenderParams(int(integrator), int(shard_mode), int(rank), int(world), 0)
+    sb, se, nt, npx = F.c_int(), F.c_int(), F.c_int(), F.c_dbl()
+    m = None
+    if mask:
+        H = F.rrt().rrt_image_height(C.byref(camera))
+        m = np.zeros((H, camera.image_width), dtype=np.uint8)
+    _check(F.rrt().rrt_shard_plan(C.byref(camera), C.byref(p), C.byref(sb), C.byref(se), C.byref(nt), C.byref(npx),
+                                  m.ctypes.data if m is not None else None))
+    out = dict(sample_begin=sb.value, sample_end=se.value, n_super_tiles=nt.value, n_pixels=npx.value)
+    if mask:
+        out["mask"] = m
+    return out
+
+
 class GpuScene:
     def __init__(self, ctx, handle):
         self.ctx, self._handle = ctx, handle
@@ -235,6 +251,10 @@ class Context:
             self.close()
         except Exception:
             pass
+
+    def set_stream(self, cuda_stream):
+        """rrt_set_stream: launch on the caller's stream (int handle; 0/None = the library's own)."""
+        _check(F.rrt().rrt_set_stream(self._h, C.c_void_p(int(cuda_stream) if cuda_stream else None)))
 
     def scene(self, desc):
         h = C.c_void_p()

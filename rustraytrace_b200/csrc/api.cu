@@ -31,7 +31,8 @@ static int fail(int st, const std::string& m) { g_err = m; return st; }
 struct rrt_ctx {
   int device = 0;
   int sm_count = 0;
-  cudaStream_t stream = nullptr;
+  cudaStream_t stream = nullptr;      // the stream every call launches on
+  cudaStream_t own_stream = nullptr;  // created by rrt_init; `stream` points elsewhere after rrt_set_stream
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   unsigned int* counter = nullptr;
   float* accum = nullptr;  // grow-only frame buffer for the host-output entry points
@@ -89,7 +90,8 @@ int rrt_init(int device, rrt_ctx** out) {
     return fail(RRT_ERR_NO_DEVICE, std::string("device '") + prop.name + "' is not sm_100-class; kernels are built for sm_100a only");
   }
   c->sm_count = prop.multiProcessorCount;
-  CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "cudaStreamCreate");
+  CK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking), "cudaStreamCreate");
+  c->stream = c->own_stream;
   for (auto& ev : c->ev) CK(cudaEventCreate(&ev), "cudaEventCreate");
   CK(cudaMalloc(&c->counter, sizeof(unsigned int)), "cudaMalloc(counter)");
   c->stats.sm_count = c->sm_count;
@@ -104,8 +106,16 @@ void rrt_shutdown(rrt_ctx* c) {
   if (c->accum) cudaFree(c->accum);
   if (c->counter) cudaFree(c->counter);
   for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
-  if (c->stream) cudaStreamDestroy(c->stream);
+  if (c->own_stream) cudaStreamDestroy(c->own_stream);
   delete c;
+}
+
+int rrt_set_stream(rrt_ctx* c, void* stream) {
+  if (!c) return fail(RRT_ERR_INVALID, "rrt_set_stream: ctx is null");
+  cudaSetDevice(c->device);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  c->stream = stream ? reinterpret_cast<cudaStream_t>(stream) : c->own_stream;
+  return RRT_OK;
 }
 
 void rrt_scene_destroy(rrt_scene* sc) {
@@ -179,20 +189,12 @@ static int check_camera(const rrt_camera* cam, const rrt_render_params* p) {
   return RRT_OK;
 }
 
-int rrt_render_device(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, const rrt_render_params* p,
-                      float* accum_dev) {
-  if (!c || !sc || !p || !accum_dev) return fail(RRT_ERR_INVALID, "rrt_render_device: null argument");
-  if (sc->ctx != c) return fail(RRT_ERR_INVALID, "scene belongs to another context");
-  int rc = check_camera(cam, p);
-  if (rc) return rc;
-  CK(cudaSetDevice(c->device), "cudaSetDevice");
-  RenderArgs A;
-  std::memset(&A, 0, sizeof A);
-  A.S = sc->dev;
+// This rank's share of the frame: which 32x32 super tiles and which sample range.
+// Pure host arithmetic, shared by rrt_render_device and rrt_shard_plan.
+static void plan_work(const rrt_camera* cam, const rrt_render_params* p, DevWork& W, DevCamera& dc, double& my_pixels) {
   DevCamera64 c64;
-  const int H = camera_initialize(cam, A.cam, c64);
+  const int H = camera_initialize(cam, dc, c64);
   const int Wd = cam->image_width;
-  DevWork& W = A.W;
   W.width = Wd; W.height = H;
   W.integrator = p->integrator;
   W.max_depth = cam->max_depth;
@@ -201,7 +203,7 @@ int rrt_render_device(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, co
   W.world = p->shard_mode == RRT_SHARD_NONE ? 1 : p->world;
   W.seed_lo = (unsigned)(p->seed & 0xffffffffu); W.seed_hi = (unsigned)(p->seed >> 32);
   int spp_eff = cam->samples_per_pixel;
-  if (p->integrator == RRT_INT_BOOK3) spp_eff = A.cam.sqrt_spp * A.cam.sqrt_spp;  // camera.rs:114-116
+  if (p->integrator == RRT_INT_BOOK3) spp_eff = dc.sqrt_spp * dc.sqrt_spp;  // camera.rs:114-116
   W.spp_eff = spp_eff;
   W.s_begin = 0; W.s_end = spp_eff;
   if (p->shard_mode == RRT_SHARD_SAMPLE) {
@@ -214,12 +216,27 @@ int rrt_render_device(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, co
   const int my_super = tr < n_super ? (n_super - tr + tw - 1) / tw : 0;
   W.n_tiles = my_super * 32;
   W.tiles_x = W.stiles_x * 4;
-  // pixels owned by this rank
-  double my_pixels = 0;
+  my_pixels = 0;
   for (int k = tr; k < n_super; k += tw) {
     int sx = k % W.stiles_x, sy = k / W.stiles_x;
     my_pixels += (double)std::min(32, Wd - sx * 32) * (double)std::min(32, H - sy * 32);
   }
+}
+
+int rrt_render_device(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, const rrt_render_params* p,
+                      float* accum_dev) {
+  if (!c || !sc || !p || !accum_dev) return fail(RRT_ERR_INVALID, "rrt_render_device: null argument");
+  if (sc->ctx != c) return fail(RRT_ERR_INVALID, "scene belongs to another context");
+  int rc = check_camera(cam, p);
+  if (rc) return rc;
+  CK(cudaSetDevice(c->device), "cudaSetDevice");
+  RenderArgs A;
+  std::memset(&A, 0, sizeof A);
+  A.S = sc->dev;
+  double my_pixels = 0;
+  plan_work(cam, p, A.W, A.cam, my_pixels);
+  DevWork& W = A.W;
+  const int Wd = W.width, H = W.height, spp_eff = W.spp_eff;
   const int n_samples = W.s_end - W.s_begin;
 
   // shared-memory prefix of the BVH and grid size
@@ -356,6 +373,29 @@ int rrt_resolve_rgb8(rrt_ctx* c, const float* accum_host, int width, int height,
   cudaFree(rgb);
   if (e != cudaSuccess) return fail(RRT_ERR_CUDA, std::string("resolve failed: ") + cudaGetErrorString(e));
   c->stats.kernel_launches = 1;
+  return RRT_OK;
+}
+
+int rrt_shard_plan(const rrt_camera* cam, const rrt_render_params* p, int32_t* sample_begin, int32_t* sample_end,
+                   int32_t* n_super_tiles, double* n_pixels, uint8_t* owner_mask) {
+  if (!p) return fail(RRT_ERR_INVALID, "rrt_shard_plan: params is null");
+  int rc = check_camera(cam, p);
+  if (rc) return rc;
+  DevWork W; DevCamera dc; double px = 0;
+  std::memset(&W, 0, sizeof W);
+  plan_work(cam, p, W, dc, px);
+  if (sample_begin) *sample_begin = W.s_begin;
+  if (sample_end) *sample_end = W.s_end;
+  if (n_super_tiles) *n_super_tiles = W.n_tiles / 32;
+  if (n_pixels) *n_pixels = px;
+  if (owner_mask) {  // W*H bytes: 1 where this rank writes the pixel
+    const bool tile = W.shard_mode == RRT_SHARD_TILE;
+    for (int y = 0; y < W.height; ++y)
+      for (int x = 0; x < W.width; ++x) {
+        int k = (y / 32) * W.stiles_x + (x / 32);
+        owner_mask[(size_t)y * W.width + x] = (!tile || k % W.world == W.rank) ? 1 : 0;
+      }
+  }
   return RRT_OK;
 }
 
