@@ -6,18 +6,13 @@ import time
 import numpy as np
 import torch
 
+import os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import rustraytrace_b200 as R
 
 F = R._ffi
-CONFIGS = {
-    "C1": ("in_one_weekend", None, dict(image_width=400, samples_per_pixel=100, max_depth=50, aspect_ratio=16 / 9)),
-    "C2": ("in_one_weekend", None, dict(image_width=1200, samples_per_pixel=500, max_depth=50)),
-    "C3a": ("the_next_week", 1, dict(image_width=1920, samples_per_pixel=1000, max_depth=50)),
-    "C3b": ("the_next_week", 3, dict(image_width=1920, samples_per_pixel=1000, max_depth=50)),
-    "C3c": ("the_next_week", 4, dict(image_width=1920, samples_per_pixel=1000, max_depth=50)),
-    "C4": ("the_next_week", 9, dict(image_width=800, samples_per_pixel=10000, max_depth=40)),
-    "C5": ("the_rest_of_your_life", None, dict(image_width=3840, samples_per_pixel=4096, max_depth=50)),
-}
+from rustraytrace_b200 import configs
+CONFIGS = configs.CONFIGS
 
 
 def main():
@@ -25,10 +20,7 @@ def main():
     names = sys.argv[2].split(",") if len(sys.argv) > 2 else list(CONFIGS)
     ctx = R.Context(0)
     for name in names:
-        book, sc, ov = CONFIGS[name]
-        ov = dict(ov)
-        ov["samples_per_pixel"] = min(ov["samples_per_pixel"], spp_cap)
-        s = R.BookScene(book, sc, overrides=ov)
+        s = configs.build(name, samples_per_pixel=min(CONFIGS[name][2]["samples_per_pixel"], spp_cap))
         gs = ctx.scene(s.desc)
         acc = torch.empty((s.height, s.width, 4), dtype=torch.float32, device="cuda")
         for _ in range(2):
