@@ -1,0 +1,126 @@
+"""CPU tier: the C-ABI libraries load, export every symbol include/*.h declares, and their
+host-only entry points (flattener check, shard plan, Philox KAT) behave.  No compute calls."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import rustraytrace_b200 as R
+
+F = R._ffi
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+ALL_SCENES = [("in_one_weekend", None), ("in_one_weekend_gpu", None), ("the_rest_of_your_life", None)] + \
+             [("the_next_week", i) for i in range(1, 10)] + [("the_next_week", None)]
+
+
+def declared(header):
+    src = open(os.path.join(ROOT, "include", header)).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(rrth?_[a-z0-9_]+)\s*\(", src)))
+
+
+@pytest.mark.parametrize("header,loader,table", [("rrt.h", F.rrt, F.RRT_SYMBOLS), ("rrt_host.h", F.rrth, F.RRTH_SYMBOLS)])
+def test_library_exports_every_declared_symbol(header, loader, table):
+    lib = loader()
+    names = declared(header)
+    assert len(names) >= 10
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in {header} but not exported"
+    assert sorted(t[0] for t in table) == names, "ctypes table and header disagree"
+
+
+def test_struct_sizes_match_header_layout():
+    assert C.sizeof(F.Hittable) == 16 + 72
+    assert C.sizeof(F.Material) == 8 + 24 + 16
+    assert C.sizeof(F.Texture) == 24 + 24 + 8
+    assert C.sizeof(F.Camera) == 8 + 16 + 24 + 8 + 72 + 16
+    assert C.sizeof(F.RenderParams) == 24
+    assert C.sizeof(F.Perlin) == 256 * 24 + 3 * 256 * 4
+
+
+def test_no_gpu_is_a_loud_error_not_a_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(R.RrtError) as e:
+        R.Context(0)
+    assert e.value.status == F.ERR_NO_DEVICE and "no CPU fallback" in str(e.value)
+
+
+def test_product_package_never_touches_the_oracle():
+    pkg = os.path.join(ROOT, "rustraytrace_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h")):
+                text = open(os.path.join(dirpath, f), errors="replace").read()
+                assert "oracle_ffi" not in text and "liboracle" not in text and "oracle/" not in text, f
+
+
+def test_philox_known_answers():
+    """Philox4x32-10 KATs from Random123's kat_vectors."""
+    def ph(c, k):
+        out = (C.c_uint32 * 4)()
+        F.rrt().rrt_philox_kat(*c, *k, out)
+        return [hex(x) for x in out]
+    assert ph((0, 0, 0, 0), (0, 0)) == ["0x6627e8d5", "0xe169c58d", "0xbc57ac4c", "0x9b00dbd8"]
+    assert ph((0xffffffff,) * 4, (0xffffffff,) * 2) == ["0x408f276d", "0x41c83b0e", "0xa20bc7c6", "0x6d5451fd"]
+    assert ph((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0)) == \
+        ["0xd16cfe09", "0x94fdcceb", "0x5001e420", "0x24126ea1"]
+
+
+@pytest.mark.parametrize("book,scene_no", ALL_SCENES)
+def test_flattener_self_check_on_every_book_scene(book, scene_no):
+    s = R.BookScene(book, scene_no, overrides=dict(image_width=64))
+    c = R.flatten_check(s.desc)
+    assert c["n_prims"] >= 1
+    if book == "the_next_week" and scene_no in (9, None):
+        assert c["n_prims"] == 2400 + 1000 + 6 + 1 and c["n_media"] == 2
+    if book == "the_next_week" and scene_no == 8:
+        assert c["n_media"] == 2 and c["n_prims"] == 6
+    if book == "the_rest_of_your_life":
+        assert c["n_prims"] == 13 and c["n_lights"] == 2
+
+
+def test_flattener_rejects_malformed_descriptions():
+    b = R.DescBuilder()
+    m = b.lambertian((0.5, 0.5, 0.5))
+    sp = b.sphere((0, 0, -1), 0.5, m)
+    with pytest.raises(R.RrtError) as e:
+        R.flatten_check(b.desc(b.list([sp, 99])))
+    assert e.value.status == F.ERR_INVALID
+    b2 = R.DescBuilder()
+    bad = b2.sphere((0, 0, 0), 1.0, 7)  # material index out of range
+    with pytest.raises(R.RrtError):
+        R.flatten_check(b2.desc(b2.list([bad])))
+    b3 = R.DescBuilder()  # empty world is legal (every ray misses)
+    assert R.flatten_check(b3.desc(b3.list([])))["n_prims"] == 0
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+def test_shard_plan_partitions_the_frame(world):
+    cam = R.make_camera(image_width=200, aspect_ratio=16 / 9, samples_per_pixel=37)
+    H = F.rrt().rrt_image_height(C.byref(cam))
+    cover = np.zeros((H, 200), dtype=np.int32)
+    got = []
+    for r in range(world):
+        t = R.shard_plan(cam, F.INT_BOOK2, F.SHARD_TILE, r, world, mask=True)
+        assert t["mask"].sum() == t["n_pixels"] and (t["sample_begin"], t["sample_end"]) == (0, 37)
+        cover += t["mask"]
+        s = R.shard_plan(cam, F.INT_BOOK2, F.SHARD_SAMPLE, r, world)
+        assert s["n_pixels"] == 200 * H
+        got.append((s["sample_begin"], s["sample_end"]))
+    assert np.all(cover == 1), "every pixel belongs to exactly one rank"
+    assert got[0][0] == 0 and got[-1][1] == 37 and all(got[i][1] == got[i + 1][0] for i in range(world - 1))
+    # book 3 shards its floor(sqrt(spp))^2 strata (camera.rs:114-116)
+    s3 = [R.shard_plan(cam, F.INT_BOOK3, F.SHARD_SAMPLE, r, world) for r in range(world)]
+    assert s3[-1]["sample_end"] == 36
+
+
+def test_image_height_truncates_like_camera_initialize():
+    # SURVEY.md §4 KAT: 400->225, 1200->675, 1920->1080 at 16/9; 800->800, 3840->3840 at 1.0
+    for w, ar, h in [(400, 16 / 9, 225), (1200, 16 / 9, 675), (1920, 16 / 9, 1080), (800, 1.0, 800), (3840, 1.0, 3840), (1, 16 / 9, 1)]:
+        cam = R.make_camera(image_width=w, aspect_ratio=ar)
+        assert F.rrt().rrt_image_height(C.byref(cam)) == h
