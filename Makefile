@@ -13,7 +13,7 @@ CXXFLAGS  := -O2 -std=c++17 -fPIC -Wall
 CSRC := $(PKG)/csrc
 HOST := $(PKG)/host
 
-all: $(PKG)/librrt.so $(PKG)/librrt_host.so oracle
+all: $(PKG)/librrt.so $(PKG)/librrt_host.so $(PKG)/bin/rrt oracle
 
 $(CSRC)/kernels.o: $(CSRC)/kernels.cu $(CSRC)/*.cuh $(CSRC)/*.h include/rrt.h
 	$(NVCC) $(NVFLAGS) -c $< -o $@
