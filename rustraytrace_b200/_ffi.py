@@ -151,7 +151,8 @@ def rrt():
     """librrt.so (CUDA kernels + C ABI)."""
     global _rrt
     if _rrt is None:
-        _rrt = _load("librrt.so", RRT_SYMBOLS)
+        # RRT_LIB: development hook to load an experimental build (scripts/build_variant.sh)
+        _rrt = _load(os.environ.get("RRT_LIB", "librrt.so"), RRT_SYMBOLS)
     return _rrt
 
 

@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -28,6 +29,7 @@ static int fail(int st, const std::string& m) { g_err = m; return st; }
     if (e_ != cudaSuccess) return fail(RRT_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e_)); \
   } while (0)
 
+struct rrt_scene;
 struct rrt_ctx {
   int device = 0;
   int sm_count = 0;
@@ -38,6 +40,7 @@ struct rrt_ctx {
   float* accum = nullptr;  // grow-only frame buffer for the host-output entry points
   size_t accum_floats = 0;
   rrt_stats stats;
+  std::vector<rrt_scene*> scenes;  // live scenes of this context (released by rrt_shutdown if the caller did not)
 };
 
 struct rrt_scene {
@@ -99,10 +102,16 @@ int rrt_init(int device, rrt_ctx** out) {
   return RRT_OK;
 }
 
+static void release_scene_memory(rrt_scene* sc);
+
 void rrt_shutdown(rrt_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
+  // scenes the caller still holds: free their device memory now and orphan the handles, so a late
+  // rrt_scene_destroy (e.g. from a garbage collector) stays harmless
+  for (rrt_scene* sc : c->scenes) release_scene_memory(sc);
+  c->scenes.clear();
   if (c->accum) cudaFree(c->accum);
   if (c->counter) cudaFree(c->counter);
   for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
@@ -118,11 +127,21 @@ int rrt_set_stream(rrt_ctx* c, void* stream) {
   return RRT_OK;
 }
 
+static void release_scene_memory(rrt_scene* sc) {
+  for (void* p : sc->allocs) cudaFree(p);
+  sc->allocs.clear();
+  sc->ctx = nullptr;
+}
+
 void rrt_scene_destroy(rrt_scene* sc) {
   if (!sc) return;
-  cudaSetDevice(sc->ctx->device);
-  cudaStreamSynchronize(sc->ctx->stream);
-  for (void* p : sc->allocs) cudaFree(p);
+  if (rrt_ctx* c = sc->ctx) {
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    for (size_t i = 0; i < c->scenes.size(); ++i)
+      if (c->scenes[i] == sc) { c->scenes.erase(c->scenes.begin() + i); break; }
+    release_scene_memory(sc);
+  }
   delete sc;
 }
 
@@ -156,8 +175,6 @@ int rrt_scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out) {
   D.n_media = (int)F.media.size();
   D.n_lights = (int)F.lights.size();
   D.has_motion = F.has_motion;
-  D.smem_nodes = 0;
-  D.smem_prims = 0;
   if (D.n_media > 5) { rrt_scene_destroy(sc); return fail(RRT_ERR_UNSUPPORTED, "more than 5 constant media"); }
   sc->n_nodes = D.n_nodes; sc->n_prims = D.n_prims; sc->n_media = D.n_media; sc->n_lights = D.n_lights;
   cudaError_t e = cudaStreamSynchronize(c->stream);  // host vectors die at return
@@ -165,6 +182,7 @@ int rrt_scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out) {
   c->stats.h2d_bytes = sc->h2d_bytes;
   c->stats.n_prims = sc->n_prims; c->stats.n_bvh_nodes = sc->n_nodes;
   c->stats.n_media = sc->n_media; c->stats.n_lights = sc->n_lights;
+  c->scenes.push_back(sc);
   *out = sc;
   return RRT_OK;
 }
@@ -226,7 +244,7 @@ static void plan_work(const rrt_camera* cam, const rrt_render_params* p, DevWork
 int rrt_render_device(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, const rrt_render_params* p,
                       float* accum_dev) {
   if (!c || !sc || !p || !accum_dev) return fail(RRT_ERR_INVALID, "rrt_render_device: null argument");
-  if (sc->ctx != c) return fail(RRT_ERR_INVALID, "scene belongs to another context");
+  if (sc->ctx != c) return fail(RRT_ERR_INVALID, "scene belongs to another (or a shut down) context");
   int rc = check_camera(cam, p);
   if (rc) return rc;
   CK(cudaSetDevice(c->device), "cudaSetDevice");
@@ -239,10 +257,7 @@ int rrt_render_device(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, co
   const int Wd = W.width, H = W.height, spp_eff = W.spp_eff;
   const int n_samples = W.s_end - W.s_begin;
 
-  // shared-memory prefix of the BVH and grid size
-  A.S.smem_nodes = std::min(A.S.n_nodes, 640);
-  size_t smem = (size_t)A.S.smem_nodes * 64;
-  int bps = render_blocks_per_sm(p->integrator, smem);
+  int bps = render_blocks_per_sm(p->integrator);
   if (bps < 1) return fail(RRT_ERR_CUDA, "kernel launch failed: render kernel does not fit on an SM");
   const int grid = c->sm_count * bps;
   const long long resident_warps = (long long)grid * (RRT_BLOCK / 32);
@@ -264,7 +279,7 @@ int rrt_render_device(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, co
   int launches = 0;
   CK(cudaEventRecord(c->ev[1], c->stream), "cudaEventRecord");
   if (W.n_tiles > 0 && n_samples > 0) {
-    CK(launch_render(A, grid, smem, c->stream), "kernel launch failed");
+    CK(launch_render(A, grid, c->stream), "kernel launch failed");
     launches = 1;
   }
   CK(cudaEventRecord(c->ev[2], c->stream), "cudaEventRecord");
@@ -325,13 +340,13 @@ int rrt_render_frame(rrt_ctx* c, const rrt_scene_desc* desc, const rrt_camera* c
 int rrt_probe(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, int precision, int32_t* prim_id, double* t) {
   if (!c || !sc || !prim_id || !t) return fail(RRT_ERR_INVALID, "rrt_probe: null argument");
   if (precision != 32 && precision != 64) return fail(RRT_ERR_INVALID, "rrt_probe: precision must be 32 or 64");
+  if (sc->ctx != c) return fail(RRT_ERR_INVALID, "scene belongs to another (or a shut down) context");
   int rc = check_camera(cam, nullptr);
   if (rc) return rc;
   CK(cudaSetDevice(c->device), "cudaSetDevice");
   ProbeArgs A;
   std::memset(&A, 0, sizeof A);
   A.S = sc->dev;
-  A.S.smem_nodes = 0;
   A.height = camera_initialize(cam, A.cam, A.cam64);
   A.width = cam->image_width;
   size_t n = (size_t)A.width * A.height;
@@ -414,9 +429,13 @@ void rrt_philox_kat(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t
 
 // ---- host-only verification of the flattener (CPU test tier) --------------------------------
 namespace {
-struct Box { float lo[3], hi[3]; };
+struct Box { double lo[3], hi[3]; };
 bool inside(const Box& c, const Box& p) {
-  for (int a = 0; a < 3; ++a) if (c.lo[a] < p.lo[a] || c.hi[a] > p.hi[a]) return false;
+  // boxes are padded and rounded independently, so allow the paddings to differ by a few ulps
+  for (int a = 0; a < 3; ++a) {
+    double tol = 2e-6 * std::max(1e-3, std::max(std::fabs(p.lo[a]), std::fabs(p.hi[a])));
+    if (c.lo[a] < p.lo[a] - tol || c.hi[a] > p.hi[a] + tol) return false;
+  }
   return true;
 }
 int as_int(float f) { int i; std::memcpy(&i, &f, 4); return i; }
@@ -449,8 +468,10 @@ extern "C" int rrt_flatten_check(const rrt_scene_desc* desc, int32_t* n_prims, i
       if (it.node < 0 || it.node >= nn) return fail(RRT_ERR_INVALID, "flatten check: node index out of range");
       if (node_seen[it.node]++) return fail(RRT_ERR_INVALID, "flatten check: node reached twice");
       const float4* n = &F.nodes[4 * it.node];
-      Box c0 = {{n[0].x, n[0].z, n[2].x}, {n[0].y, n[0].w, n[2].y}};
-      Box c1 = {{n[1].x, n[1].z, n[2].z}, {n[1].y, n[1].w, n[2].w}};
+      Box c0 = {{(double)n[0].x - n[0].y, (double)n[0].z - n[0].w, (double)n[2].x - n[2].y},
+                {(double)n[0].x + n[0].y, (double)n[0].z + n[0].w, (double)n[2].x + n[2].y}};
+      Box c1 = {{(double)n[1].x - n[1].y, (double)n[1].z - n[1].w, (double)n[2].z - n[2].w},
+                {(double)n[1].x + n[1].y, (double)n[1].z + n[1].w, (double)n[2].z + n[2].w}};
       if (it.has_box && (!inside(c0, it.box) || !inside(c1, it.box)))
         return fail(RRT_ERR_INVALID, "flatten check: child box escapes its parent");
       int refs[2] = {as_int(n[3].x), as_int(n[3].y)};

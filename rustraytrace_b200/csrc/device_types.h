@@ -4,12 +4,13 @@
 // flat arrays:
 //   prims   : one 64-byte record (4 x float4) per world-space leaf primitive, stored in BVH-leaf
 //             order so a leaf is a contiguous run; within a leaf spheres come first, then quads.
-//   nodes   : one 64-byte record per inner BVH node holding BOTH children's boxes, breadth-first,
-//             so the top of the tree can be staged in shared memory as a prefix.
+//   nodes   : one 64-byte record per inner BVH node holding BOTH children's boxes, breadth-first
+//             (the hot top of the tree is contiguous and stays L1-resident).
 //   bprims  : boundary primitives of constant media (same record format), outside the BVH.
 //   prims64 : f64 twin of prims (16 doubles per record) for the probe kernel.
 #pragma once
 #include <stdint.h>
+
 
 #if defined(__CUDACC__)
 #include <cuda_runtime.h>
@@ -32,8 +33,10 @@ enum PrimKind { PRIM_SPHERE = 0, PRIM_QUAD = 1 };
 enum PrimFlags { PF_UV_ROTATED = 1 };
 
 // ---- BVH inner node (float4 n[4]) ------------------------------------------------------------
-// n0 = (c0.lo.x, c0.hi.x, c0.lo.y, c0.hi.y)   n1 = (c1.lo.x, c1.hi.x, c1.lo.y, c1.hi.y)
-// n2 = (c0.lo.z, c0.hi.z, c1.lo.z, c1.hi.z)   n3 = (ref0, ref1, 0, 0) as int bits
+// boxes are (center c, half-extent e): the slab planes are c*(1/d) - o*(1/d) -+ e*|1/d|, three FMAs
+// per axis and no min/max pairs (the ALU pipe, not the FMA pipe, was the busy one: profiles/).
+// n0 = (c0.c.x, c0.e.x, c0.c.y, c0.e.y)   n1 = (c1.c.x, c1.e.x, c1.c.y, c1.e.y)
+// n2 = (c0.c.z, c0.e.z, c1.c.z, c1.e.z)   n3 = (ref0, ref1, 0, 0) as int bits
 // ref >= 0: inner node index.  ref < 0: leaf, ~ref = (first << 8) | (n_spheres << 4) | n_quads.
 static const int LEAF_MAX_PER_KIND = 15;
 inline
@@ -119,8 +122,6 @@ struct DevScene {
   int root_ref;
   int n_nodes, n_prims, n_media, n_lights;
   int has_motion;    // any sphere with dc != 0
-  int smem_nodes;    // how many leading nodes the kernel stages in shared memory
-  int smem_prims;    // how many leading prims are staged after them
 };
 
 // One launch's share of the frame.

@@ -435,11 +435,6 @@ struct Builder {
   }
 };
 
-inline float round_down(double v) {
-  float f = (float)v;
-  if ((double)f > v) f = std::nextafterf(f, -std::numeric_limits<float>::infinity());
-  return f;
-}
 inline float round_up(double v) {
   float f = (float)v;
   if ((double)f < v) f = std::nextafterf(f, std::numeric_limits<float>::infinity());
@@ -477,13 +472,16 @@ void emit_prim64(const BakedPrim& p, std::vector<double>& out) {
   out.insert(out.end(), q, q + 16);
 }
 
-// conservative f32 box: outward rounding plus a relative pad that covers the f32 slab arithmetic
-void box32(const double* lo, const double* hi, float* flo, float* fhi) {
+// conservative f32 box as (center, half-extent): the half-extent is rounded up from the padded
+// f64 box, the pad being relative so that it covers the f32 slab arithmetic
+void box32(const double* lo, const double* hi, float* fc, float* fh) {
   for (int a = 0; a < 3; ++a) {
     double m = std::max(std::fabs(lo[a]), std::fabs(hi[a]));
     double pad = 4e-7 * m + 1e-7 * (hi[a] - lo[a]);
-    flo[a] = round_down(lo[a] - pad);
-    fhi[a] = round_up(hi[a] + pad);
+    float c = (float)(0.5 * (lo[a] + hi[a]));
+    double need = std::max((hi[a] + pad) - (double)c, (double)c - (lo[a] - pad));
+    fc[a] = c;
+    fh[a] = round_up(need);
   }
 }
 
@@ -684,13 +682,13 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
   for (int n : bfs) {
     const BNode& l = B.nodes[B.nodes[n].left];
     const BNode& r = B.nodes[B.nodes[n].right];
-    float llo[3], lhi[3], rlo[3], rhi[3];
-    box32(l.lo, l.hi, llo, lhi); box32(r.lo, r.hi, rlo, rhi);
+    float lc[3], lh[3], rc[3], rh[3];
+    box32(l.lo, l.hi, lc, lh); box32(r.lo, r.hi, rc, rh);
     int ref0 = l.left >= 0 ? inner_index[B.nodes[n].left] : leaf_ref[B.nodes[n].left];
     int ref1 = r.left >= 0 ? inner_index[B.nodes[n].right] : leaf_ref[B.nodes[n].right];
-    float4 a; a.x = llo[0]; a.y = lhi[0]; a.z = llo[1]; a.w = lhi[1];
-    float4 b; b.x = rlo[0]; b.y = rhi[0]; b.z = rlo[1]; b.w = rhi[1];
-    float4 c; c.x = llo[2]; c.y = lhi[2]; c.z = rlo[2]; c.w = rhi[2];
+    float4 a; a.x = lc[0]; a.y = lh[0]; a.z = lc[1]; a.w = lh[1];
+    float4 b; b.x = rc[0]; b.y = rh[0]; b.z = rc[1]; b.w = rh[1];
+    float4 c; c.x = lc[2]; c.y = lh[2]; c.z = rc[2]; c.w = rh[2];
     out.nodes.push_back(a); out.nodes.push_back(b); out.nodes.push_back(c);
     out.nodes.push_back(i4(ref0, ref1, 0, 0));
   }

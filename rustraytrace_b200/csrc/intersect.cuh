@@ -122,10 +122,24 @@ __device__ inline float safe_rcp(float d) {
   return 1.0f / (ad > 1e-30f ? d : copysignf(1e-30f, d));
 }
 
+// Aabb::hit (aabb.rs:52-84) for both children of a node.  Boxes are (center, half-extent), so the
+// two plane distances of an axis are tc -+ e*|1/d| with tc = c*(1/d) - o*(1/d): 3 FMAs per axis and
+// child, then one 3-input max/min per interval end — no per-axis min/max pairs.
+__device__ __forceinline__ void slab2(float4 n0, float4 n1, float4 n2, float idx, float idy, float idz,
+                                      float oodx, float oody, float oodz, float tmin, float tmax,
+                                      float& near0, float& far0, float& near1, float& far1) {
+  const float ax = fabsf(idx), ay = fabsf(idy), az = fabsf(idz);
+  const float t0x = fmaf(n0.x, idx, -oodx), t0y = fmaf(n0.z, idy, -oody), t0z = fmaf(n2.x, idz, -oodz);
+  const float t1x = fmaf(n1.x, idx, -oodx), t1y = fmaf(n1.z, idy, -oody), t1z = fmaf(n2.z, idz, -oodz);
+  near0 = fmaxf(fmaxf(fmaf(-n0.y, ax, t0x), fmaf(-n0.w, ay, t0y)), fmaxf(fmaf(-n2.y, az, t0z), tmin));
+  far0 = fminf(fminf(fmaf(n0.y, ax, t0x), fmaf(n0.w, ay, t0y)), fminf(fmaf(n2.y, az, t0z), tmax));
+  near1 = fmaxf(fmaxf(fmaf(-n1.y, ax, t1x), fmaf(-n1.w, ay, t1y)), fmaxf(fmaf(-n2.w, az, t1z), tmin));
+  far1 = fminf(fminf(fmaf(n1.y, ax, t1x), fmaf(n1.w, ay, t1y)), fminf(fmaf(n2.w, az, t1z), tmax));
+}
+
 // World::hit for the render kernel: closest hit in (tmin, +inf).
-// s_nodes: leading n_smem nodes staged in shared memory (breadth-first prefix).
-__device__ inline void world_hit32(const DevScene& S, const float4* __restrict__ s_nodes, const Ray32& r,
-                                   float tmin, int skip, Hit32& h) {
+// Nodes and primitives come through L1 (ld.global.nc).
+__device__ inline void world_hit32(const DevScene& S, const Ray32& r, float tmin, int skip, Hit32& h) {
   const float a = dot(r.d, r.d);
   const float inv_a = 1.0f / a;
   const bool motion = S.has_motion != 0;
@@ -138,27 +152,19 @@ __device__ inline void world_hit32(const DevScene& S, const float4* __restrict__
   const float oodx = r.o.x * idx, oody = r.o.y * idy, oodz = r.o.z * idz;
   int stack[RRT_STACK];
   int sp = 0;
-  const int n_smem = S.smem_nodes;
+  // while-while traversal (Aila & Laine 2009): every lane first descends through inner nodes until
+  // it holds a leaf, then the warp reconverges and processes leaves together; the single mixed
+  // loop this replaces ran the inner-node and the leaf body serially whenever lanes disagreed
+  // (warp execution efficiency 42 % in profiles/ncu_r01_*).  A finer-grained lane state machine
+  // that voted on the next step every iteration was measured 35 % slower (vote overhead).
   for (;;) {
-    if (cur >= 0) {
+    bool done = false;
+    while (cur >= 0) {
       float4 n0, n1, n2, n3;
-      if (cur < n_smem) {
-        n0 = s_nodes[4 * cur]; n1 = s_nodes[4 * cur + 1]; n2 = s_nodes[4 * cur + 2]; n3 = s_nodes[4 * cur + 3];
-      } else {
-        const float4* g = S.nodes + 4 * cur;
-        n0 = ldg4(g); n1 = ldg4(g + 1); n2 = ldg4(g + 2); n3 = ldg4(g + 3);
-      }
-      // Aabb::hit (aabb.rs:52-84) for both children; t = lo * (1/d) - o * (1/d)
-      float c0x0 = fmaf(n0.x, idx, -oodx), c0x1 = fmaf(n0.y, idx, -oodx);
-      float c0y0 = fmaf(n0.z, idy, -oody), c0y1 = fmaf(n0.w, idy, -oody);
-      float c0z0 = fmaf(n2.x, idz, -oodz), c0z1 = fmaf(n2.y, idz, -oodz);
-      float c1x0 = fmaf(n1.x, idx, -oodx), c1x1 = fmaf(n1.y, idx, -oodx);
-      float c1y0 = fmaf(n1.z, idy, -oody), c1y1 = fmaf(n1.w, idy, -oody);
-      float c1z0 = fmaf(n2.z, idz, -oodz), c1z1 = fmaf(n2.w, idz, -oodz);
-      float near0 = fmaxf(fmaxf(fminf(c0x0, c0x1), fminf(c0y0, c0y1)), fmaxf(fminf(c0z0, c0z1), tmin));
-      float far0 = fminf(fminf(fmaxf(c0x0, c0x1), fmaxf(c0y0, c0y1)), fminf(fmaxf(c0z0, c0z1), h.t));
-      float near1 = fmaxf(fmaxf(fminf(c1x0, c1x1), fminf(c1y0, c1y1)), fmaxf(fminf(c1z0, c1z1), tmin));
-      float far1 = fminf(fminf(fmaxf(c1x0, c1x1), fmaxf(c1y0, c1y1)), fminf(fmaxf(c1z0, c1z1), h.t));
+      const float4* g = S.nodes + 4 * cur;
+      n0 = ldg4(g); n1 = ldg4(g + 1); n2 = ldg4(g + 2); n3 = ldg4(g + 3);
+      float near0, far0, near1, far1;
+      slab2(n0, n1, n2, idx, idy, idz, oodx, oody, oodz, tmin, h.t, near0, far0, near1, far1);
       bool hit0 = near0 <= far0 * 1.0000004f;
       bool hit1 = near1 <= far1 * 1.0000004f;
       int r0 = __float_as_int(n3.x), r1 = __float_as_int(n3.y);
@@ -166,13 +172,17 @@ __device__ inline void world_hit32(const DevScene& S, const float4* __restrict__
         if (near1 < near0) { int t = r0; r0 = r1; r1 = t; }
         if (sp < RRT_STACK) stack[sp++] = r1;
         cur = r0;
-        continue;
+      } else if (hit0) {
+        cur = r0;
+      } else if (hit1) {
+        cur = r1;
+      } else {
+        if (sp == 0) { done = true; break; }
+        cur = stack[--sp];
       }
-      if (hit0) { cur = r0; continue; }
-      if (hit1) { cur = r1; continue; }
-    } else {
-      leaf_hit32(S.prims, ~cur, r, a, inv_a, tmin, skip, motion, h);
     }
+    if (done) break;
+    leaf_hit32(S.prims, ~cur, r, a, inv_a, tmin, skip, motion, h);
     if (sp == 0) break;
     cur = stack[--sp];
   }
@@ -287,12 +297,13 @@ __device__ inline void world_hit64(const DevScene& S, V3d o, V3d d, double tmin,
     if (cur >= 0) {
       const float4* g = S.nodes + 4 * cur;
       float4 n0 = ldg4(g), n1 = ldg4(g + 1), n2 = ldg4(g + 2), n3 = ldg4(g + 3);
-      double c0x0 = ((double)n0.x - o.x) * idx, c0x1 = ((double)n0.y - o.x) * idx;
-      double c0y0 = ((double)n0.z - o.y) * idy, c0y1 = ((double)n0.w - o.y) * idy;
-      double c0z0 = ((double)n2.x - o.z) * idz, c0z1 = ((double)n2.y - o.z) * idz;
-      double c1x0 = ((double)n1.x - o.x) * idx, c1x1 = ((double)n1.y - o.x) * idx;
-      double c1y0 = ((double)n1.z - o.y) * idy, c1y1 = ((double)n1.w - o.y) * idy;
-      double c1z0 = ((double)n2.z - o.z) * idz, c1z1 = ((double)n2.w - o.z) * idz;
+      // (center, half-extent) -> planes; the boxes are conservative supersets of the reference's
+      double c0x0 = ((double)n0.x - (double)n0.y - o.x) * idx, c0x1 = ((double)n0.x + (double)n0.y - o.x) * idx;
+      double c0y0 = ((double)n0.z - (double)n0.w - o.y) * idy, c0y1 = ((double)n0.z + (double)n0.w - o.y) * idy;
+      double c0z0 = ((double)n2.x - (double)n2.y - o.z) * idz, c0z1 = ((double)n2.x + (double)n2.y - o.z) * idz;
+      double c1x0 = ((double)n1.x - (double)n1.y - o.x) * idx, c1x1 = ((double)n1.x + (double)n1.y - o.x) * idx;
+      double c1y0 = ((double)n1.z - (double)n1.w - o.y) * idy, c1y1 = ((double)n1.z + (double)n1.w - o.y) * idy;
+      double c1z0 = ((double)n2.z - (double)n2.w - o.z) * idz, c1z1 = ((double)n2.z + (double)n2.w - o.z) * idz;
       double near0 = fmax(fmax(fmin(c0x0, c0x1), fmin(c0y0, c0y1)), fmax(fmin(c0z0, c0z1), tmin));
       double far0 = fmin(fmin(fmax(c0x0, c0x1), fmax(c0y0, c0y1)), fmin(fmax(c0z0, c0z1), h.t));
       double near1 = fmax(fmax(fmin(c1x0, c1x1), fmin(c1y0, c1y1)), fmax(fmin(c1z0, c1z1), tmin));

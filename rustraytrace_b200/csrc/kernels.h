@@ -5,7 +5,9 @@
 #include "device_types.h"
 
 #define RRT_BLOCK 128
-#define RRT_MIN_BLOCKS 4
+#ifndef RRT_MIN_BLOCKS
+#define RRT_MIN_BLOCKS 6  // 80 registers/thread, no spills; 24 warps per SM
+#endif
 
 namespace rrt {
 
@@ -26,8 +28,8 @@ struct ProbeArgs {
   double* t;
 };
 
-cudaError_t launch_render(const RenderArgs& A, int grid, size_t smem, cudaStream_t st);
-int render_blocks_per_sm(int integrator, size_t smem);
+cudaError_t launch_render(const RenderArgs& A, int grid, cudaStream_t st);
+int render_blocks_per_sm(int integrator);
 cudaError_t launch_probe(const ProbeArgs& A, int precision, cudaStream_t st);
 cudaError_t launch_probe64(const ProbeArgs& A, cudaStream_t st);  // probe64.cu (-fmad=false)
 cudaError_t launch_resolve(const float* accum, int n, int spp, unsigned char* rgb, cudaStream_t st);

@@ -146,3 +146,17 @@ def test_errors_are_reported_not_fatal(ctx):
     cam = R.make_camera(image_width=0)
     with pytest.raises(R.RrtError):
         ctx.render(gs, cam, F.INT_BOOK1)
+
+
+def test_teardown_in_either_order_is_safe():
+    """rrt_shutdown releases scenes the caller still holds; a late rrt_scene_destroy is harmless."""
+    s = R.BookScene("in_one_weekend", overrides=dict(image_width=64, samples_per_pixel=2, max_depth=5))
+    c = R.Context(0)
+    gs = c.scene(s.desc)
+    c.render(gs, s.camera, s.integrator)
+    c.close()
+    gs.close()
+    c2 = R.Context(0)
+    g2 = c2.scene(s.desc)
+    g2.close()
+    c2.close()
