@@ -294,6 +294,24 @@ def main():
             v, sample, f_live, _, _ = cpu_sample(args.config, args.cpu_seconds, os.cpu_count() or 1)
             cpu = {"value": round(v, 4), "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port", "sample": sample,
                    "flops_per_path_live": round(f_live, 1)}
+        ref_cuda = None
+        if n_gpus == 1 and not args.no_cpu and scene.integrator == F.INT_BOOK1:
+            # the reference's existing src/cuda path, same scene, same box, its own launch shape
+            # (oracle/_ref/libref_cuda.so, tests/ref_cuda_ffi.py); it supports book-1 scenes only
+            try:
+                import ref_cuda_ffi as RC
+                if RC.available():
+                    rs = configs.build(args.config, samples_per_pixel=min(128, st["spp_effective"]))
+                    RC.render(configs.build(args.config, samples_per_pixel=4))   # warm-up
+                    racc, rms, rpasses = RC.render(rs)
+                    rpaths = float(W) * H * rs.camera.samples_per_pixel
+                    rm = racc[..., :3].sum(axis=(0, 1)) / racc[..., 3].sum()
+                    ref_cuda = {"value": round(rpaths / rms / 1e3, 2), "unit": UNIT, "kernel_ms": round(rms, 3),
+                                "sample": f"full frame at {rs.camera.samples_per_pixel} spp, {rpasses} pass(es) of <=256 spp, 8x8 blocks, sync per pass",
+                                "what": "reference src/cuda/mod.rs kernel (brute-force spheres, f32, xorshift32), compiled for sm_100a",
+                                "frame_mean_radiance": [round(float(x), 5) for x in rm]}
+            except Exception as e:  # the comparison arm must never take the bench down
+                ref_cuda = {"unavailable": repr(e)}
         sm_max = float(peaks.get("sm_max_mhz", 1965.0))
         peak_tf = sm_count * SM_LANES * 2 * sm_max * 1e6 / 1e12
         # dominant kernel = render_kernel: algorithmic flops per launch / its mean launch duration
@@ -316,7 +334,7 @@ def main():
                            "max_depth": scene.camera.max_depth, "scene_seed": hex(configs.SCENE_SEED),
                            "sharding": "none" if n_gpus == 1 else f"{mode}-range over {n_gpus} ranks + NCCL sum-reduce to rank 0",
                            "l2": "flushed between steps (256 MiB fill)", "prims": st["n_prims"], "bvh_nodes": st["n_bvh_nodes"]},
-                "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks,
+                "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu, "ref_cuda_kernel": ref_cuda, "clocks": clocks,
                 "wall_s": round(wall_s, 3), "frame_mean_radiance": frame_mean}
         if args.spp > 0:
             line["config"]["diagnostic_spp_override"] = args.spp
