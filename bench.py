@@ -332,7 +332,7 @@ def main():
                 "config": {"workload": workload_name(args.config, n_gpus),
                            "key": args.config, "width": W, "height": H, "spp": st["spp_effective"],
                            "max_depth": scene.camera.max_depth, "scene_seed": hex(configs.SCENE_SEED),
-                           "sharding": "none" if n_gpus == 1 else f"{mode}-range over {n_gpus} ranks + NCCL sum-reduce to rank 0",
+                           "sharding": "none" if n_gpus == 1 else ("sample ranges" if mode == "sample" else "interleaved 32x32 tiles") + f" over {n_gpus} ranks + NCCL sum-reduce to rank 0",
                            "l2": "flushed between steps (256 MiB fill)", "prims": st["n_prims"], "bvh_nodes": st["n_bvh_nodes"]},
                 "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu, "ref_cuda_kernel": ref_cuda, "clocks": clocks,
                 "wall_s": round(wall_s, 3), "frame_mean_radiance": frame_mean}
