@@ -27,8 +27,9 @@ $(CSRC)/flatten.o: $(CSRC)/flatten.cpp $(CSRC)/flatten.hpp $(CSRC)/device_types.
 $(PKG)/librrt.so: $(CSRC)/kernels.o $(CSRC)/probe64.o $(CSRC)/api.o $(CSRC)/flatten.o
 	$(NVCC) -shared -o $@ $^ -cudart shared
 
-$(PKG)/librrt_host.so: $(HOST)/books.cpp $(HOST)/rtw_image.cpp $(HOST)/render_io.cpp $(HOST)/*.hpp include/*.h
-	$(CXX) $(CXXFLAGS) -shared -o $@ $(HOST)/books.cpp $(HOST)/rtw_image.cpp $(HOST)/render_io.cpp
+HOST_SRC := $(HOST)/books.cpp $(HOST)/rtw_image.cpp $(HOST)/jpeg_decode.cpp $(HOST)/render_io.cpp
+$(PKG)/librrt_host.so: $(HOST_SRC) $(HOST)/*.hpp include/*.h
+	$(CXX) $(CXXFLAGS) -shared -o $@ $(HOST_SRC)
 
 $(PKG)/bin/rrt: $(HOST)/main.cpp $(PKG)/librrt.so $(PKG)/librrt_host.so
 	mkdir -p $(PKG)/bin

@@ -74,6 +74,13 @@ int rrth_write_ppm_from_accum(const char* path, int width, int height, const flo
 /* Same text format from already-resolved RGB8 (the bytes rrt_resolve_rgb8 produces). */
 int rrth_write_ppm_rgb8(const char* path, int width, int height, const uint8_t* rgb);
 
+/* RtwImage::new + load (the_rest_of_your_life/rtw_image.rs:10-67): the same search order
+ * ($RTW_IMAGES, cwd, images/ in up to six parents; extra_dir first) and a native decode (baseline JPEG,
+ * binary PPM).  rgb may be NULL to query the size; returns 0, -1 (not found / undecodable), -2
+ * (rgb_capacity too small). */
+int rrth_load_image(const char* filename, const char* extra_dir, int32_t* width, int32_t* height,
+                    uint8_t* rgb, uint64_t rgb_capacity);
+
 /* Known-answer hooks for the scene RNG (tests only). */
 uint64_t rrth_rng_kat_state1234(int n);          /* n-th output of xoshiro256++ from state {1,2,3,4} */
 double rrth_rng_kat_seeded_f64(uint64_t seed, int n); /* n-th random_double() after seed_from_u64 */

@@ -123,6 +123,7 @@ RRTH_SYMBOLS = [
     ("rrth_scene_free", None, [VP]),
     ("rrth_write_ppm_from_accum", c_int, [C.c_char_p, c_int, c_int, VP, C.c_uint32]),
     ("rrth_write_ppm_rgb8", c_int, [C.c_char_p, c_int, c_int, VP]),
+    ("rrth_load_image", c_int, [C.c_char_p, C.c_char_p, C.POINTER(c_int), C.POINTER(c_int), VP, C.c_uint64]),
     ("rrth_rng_kat_state1234", C.c_uint64, [c_int]),
     ("rrth_rng_kat_seeded_f64", c_dbl, [C.c_uint64, c_int]),
     ("rrth_last_error", C.c_char_p, []),

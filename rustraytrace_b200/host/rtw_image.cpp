@@ -4,13 +4,15 @@
 // current directory and up to six parents (:14-32).  An extra directory handed in by the caller
 // is tried first (the Python package passes the repo's images/ so tests do not depend on cwd).
 //
-// Decoding: the reference uses image 0.25.9 -> zune-jpeg 0.5.12 (Cargo.lock).  This image has no
-// JPEG headers for C++; a candidate "<file>" is therefore loaded from a decoded sibling
-// "<stem>.ppm" (binary P6, written from the same JPEG by __graft_entry__.build() through
-// PIL/libjpeg-turbo).  Texel parity against zune-jpeg is unpinned (±1-2 LSB from IDCT/upsampling).
+// Decoding: the reference uses image 0.25.9 -> zune-jpeg 0.5.12 (Cargo.lock).  Here a candidate file
+// is decoded natively: baseline JPEG by jpeg_decode.cpp, binary PPM (P6) by the reader below; a
+// decoded sibling "<stem>.ppm" is accepted as well.  Texel parity against zune-jpeg is unpinned
+// (+-1 LSB from IDCT rounding).
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <string>
+#include <vector>
 
 #include "scene_builder.hpp"
 
@@ -44,14 +46,35 @@ static bool read_ppm_p6(const std::string& path, LoadedImage& out) {
   return true;
 }
 
+static bool read_file(const std::string& path, std::vector<uint8_t>& bytes) {
+  FILE* f = std::fopen(path.c_str(), "rb");
+  if (!f) return false;
+  std::fseek(f, 0, SEEK_END);
+  long n = std::ftell(f);
+  std::fseek(f, 0, SEEK_SET);
+  bool ok = n > 0;
+  if (ok) { bytes.resize((size_t)n); ok = std::fread(bytes.data(), 1, bytes.size(), f) == bytes.size(); }
+  std::fclose(f);
+  return ok;
+}
+
 // RtwImage::load (:57-67) for one candidate path.
 static bool load_candidate(const std::string& path, LoadedImage& out) {
+  std::vector<uint8_t> bytes;
+  if (read_file(path, bytes) && bytes.size() > 3) {
+    if (bytes[0] == 0xFF && bytes[1] == 0xD8) {
+      std::string err;
+      if (decode_jpeg(bytes, out, err)) return true;
+      std::fprintf(stderr, "ERROR: '%s': %s\n", path.c_str(), err.c_str());
+    } else if (read_ppm_p6(path, out)) {
+      return true;
+    }
+  }
   size_t dot = path.find_last_of('.');
   size_t slash = path.find_last_of('/');
   std::string stem = (dot != std::string::npos && (slash == std::string::npos || dot > slash))
                          ? path.substr(0, dot) : path;
-  if (read_ppm_p6(stem + ".ppm", out)) return true;
-  return read_ppm_p6(path, out);  // the candidate itself may already be a P6 file
+  return stem + ".ppm" != path && read_ppm_p6(stem + ".ppm", out);
 }
 
 bool load_rtw_image(const std::string& filename, const char* extra_dir, LoadedImage& out) {
@@ -73,3 +96,17 @@ bool load_rtw_image(const std::string& filename, const char* extra_dir, LoadedIm
 }
 
 }  // namespace rrt_host
+
+// C export (include/rrt_host.h): the loader by itself, for tests and tools.
+extern "C" int rrth_load_image(const char* filename, const char* extra_dir, int32_t* width, int32_t* height,
+                               uint8_t* rgb, uint64_t rgb_capacity) {
+  rrt_host::LoadedImage im;
+  if (!filename || !rrt_host::load_rtw_image(filename, extra_dir, im)) return -1;
+  if (width) *width = im.width;
+  if (height) *height = im.height;
+  if (rgb) {
+    if (rgb_capacity < im.rgb.size()) return -2;
+    std::memcpy(rgb, im.rgb.data(), im.rgb.size());
+  }
+  return 0;
+}

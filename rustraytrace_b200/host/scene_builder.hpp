@@ -38,6 +38,7 @@ struct LoadedImage {
   std::vector<uint8_t> rgb;
 };
 bool load_rtw_image(const std::string& filename, const char* extra_dir, LoadedImage& out);
+bool decode_jpeg(const std::vector<uint8_t>& file, LoadedImage& out, std::string& err);  // jpeg_decode.cpp
 
 struct SceneBuilder {
   std::vector<rrt_hittable> hittables;

@@ -157,3 +157,47 @@ def test_ppm_writer_matches_render_io(tmp_path):
     p2 = str(tmp_path / "p.ppm")
     assert F.rrth().rrth_write_ppm_rgb8(p2.encode(), 7, 5, got.ctypes.data) == 0
     assert open(p2).read() == open(path).read()
+
+
+def test_native_jpeg_decode_matches_libjpeg():
+    """rtw_image.rs:57-67 decodes with zune-jpeg; our baseline decoder (host/jpeg_decode.cpp) is checked
+    against libjpeg-turbo (PIL) on the reference's one asset: same size, texels within a few LSB."""
+    from PIL import Image
+    w, h = F.c_int(), F.c_int()
+    assert F.rrth().rrth_load_image(b"earthmap.jpg", F.IMAGE_DIR.encode(), C.byref(w), C.byref(h), None, 0) == 0
+    assert (w.value, h.value) == (1024, 512)
+    buf = np.zeros((512, 1024, 3), dtype=np.uint8)
+    assert F.rrth().rrth_load_image(b"earthmap.jpg", F.IMAGE_DIR.encode(), C.byref(w), C.byref(h), buf.ctypes.data, buf.nbytes) == 0
+    ref = np.asarray(Image.open(os.path.join(F.IMAGE_DIR, "earthmap.jpg")).convert("RGB")).astype(int)
+    d = np.abs(buf.astype(int) - ref)
+    assert d.max() <= 3 and d.mean() < 0.05
+    assert np.allclose(buf.mean(axis=(0, 1)), [81.10, 85.93, 104.10], atol=0.05)      # SURVEY.md §2 #10
+    assert F.rrth().rrth_load_image(b"earthmap.jpg", F.IMAGE_DIR.encode(), None, None, buf.ctypes.data, 10) == -2
+    assert F.rrth().rrth_load_image(b"no_such_image.jpg", None, None, None, None, 0) == -1
+
+
+def test_jpeg_decoder_handles_subsampling_restarts_and_grey(tmp_path):
+    from PIL import Image
+    rng = np.random.default_rng(3)
+    yy, xx = np.mgrid[0:70, 0:93]
+    img = np.stack([(xx * 2) % 256, (yy * 3) % 256, ((xx + yy) * 2) % 256], axis=-1).astype(np.uint8)
+    img = (img // 2 + rng.integers(0, 20, img.shape)).astype(np.uint8)
+    w, h = F.c_int(), F.c_int()
+    for name, kw, tol in [("s444.jpg", dict(subsampling=0), 4), ("s420.jpg", dict(subsampling=2), 64),
+                          ("s422.jpg", dict(subsampling=1), 64), ("rst.jpg", dict(subsampling=0, restart_marker_blocks=3), 4)]:
+        p = str(tmp_path / name)
+        Image.fromarray(img).save(p, quality=92, **kw)
+        buf = np.zeros((70, 93, 3), dtype=np.uint8)
+        assert F.rrth().rrth_load_image(p.encode(), None, C.byref(w), C.byref(h), buf.ctypes.data, buf.nbytes) == 0, name
+        assert (w.value, h.value) == (93, 70)
+        ref = np.asarray(Image.open(p).convert("RGB")).astype(int)
+        d = np.abs(buf.astype(int) - ref)
+        assert d.max() <= tol and d.mean() < (0.2 if tol == 4 else 3.0), (name, d.max(), d.mean())   # subsampled: no fancy upsampling here
+    p = str(tmp_path / "grey.jpg")
+    Image.fromarray(img[..., 0]).save(p, quality=95)
+    buf = np.zeros((70, 93, 3), dtype=np.uint8)
+    assert F.rrth().rrth_load_image(p.encode(), None, C.byref(w), C.byref(h), buf.ctypes.data, buf.nbytes) == 0
+    assert np.abs(buf[..., 0].astype(int) - np.asarray(Image.open(p)).astype(int)).max() <= 2 and np.array_equal(buf[..., 0], buf[..., 2])
+    p = str(tmp_path / "prog.jpg")
+    Image.fromarray(img).save(p, progressive=True)
+    assert F.rrth().rrth_load_image(p.encode(), None, None, None, None, 0) == -1       # rejected loudly, not mis-decoded
