@@ -124,3 +124,15 @@ def test_image_height_truncates_like_camera_initialize():
     for w, ar, h in [(400, 16 / 9, 225), (1200, 16 / 9, 675), (1920, 16 / 9, 1080), (800, 1.0, 800), (3840, 1.0, 3840), (1, 16 / 9, 1)]:
         cam = R.make_camera(image_width=w, aspect_ratio=ar)
         assert F.rrt().rrt_image_height(C.byref(cam)) == h
+
+
+def test_rust_binding_declares_every_entry_point():
+    """bindings/rrt_ffi.rs (unbuilt here: no rustc) must name every function of include/rrt.h."""
+    rs = open(os.path.join(ROOT, "bindings", "rrt_ffi.rs")).read()
+    for n in declared("rrt.h"):
+        assert re.search(r"pub fn %s\(" % n, rs), f"{n} missing from bindings/rrt_ffi.rs"
+    # #[repr(C)] mirrors carry the same field counts as the ctypes mirrors (which are size-checked above)
+    for rust, py in [("RrtHittable", F.Hittable), ("RrtMaterial", F.Material), ("RrtTexture", F.Texture),
+                     ("RrtCamera", F.Camera), ("RrtRenderParams", F.RenderParams), ("RrtStats", F.Stats)]:
+        body = re.search(r"pub struct %s \{(.*?)\}" % rust, rs, re.S).group(1)
+        assert len(re.findall(r"pub \w+:", body)) == len(py._fields_), rust

@@ -1,0 +1,51 @@
+"""GPU tier: the `rrt` command line (host/main.cpp, mirror of src/main.rs:14-99) end to end."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import rustraytrace_b200 as R
+
+pytestmark = pytest.mark.gpu
+RRT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "rustraytrace_b200", "bin", "rrt")
+
+
+def read_p3(text):
+    tok = text.split()
+    assert tok[0] == "P3" and tok[3] == "255"
+    w, h = int(tok[1]), int(tok[2])
+    return np.array(tok[4:], dtype=np.int64).reshape(h, w, 3)
+
+
+def test_cli_renders_the_same_image_as_the_library(tmp_path):
+    p = subprocess.run([RRT, "--cuda", "the_next_week", "3", "--width", "96", "--spp", "64", "--depth", "10", "--sample-seed", "5"],
+                       capture_output=True, text=True, timeout=120)
+    assert p.returncode == 0, p.stderr
+    img = read_p3(p.stdout)
+    assert img.shape == (54, 96, 3)
+    s = R.BookScene("the_next_week", 3, overrides=dict(image_width=96, samples_per_pixel=64, max_depth=10))
+    ctx = R.Context(0)
+    gs = ctx.scene(s.desc)
+    want = ctx.resolve(ctx.render(gs, s.camera, s.integrator, seed=5), 64)
+    assert np.array_equal(img, want)
+    gs.close(); ctx.close()
+
+
+def test_cli_book_aliases_probe_and_errors(tmp_path):
+    out = str(tmp_path / "p.txt")
+    p = subprocess.run([RRT, "rest", "--width", "32", "--probe", "-o", out], capture_output=True, text=True, timeout=120)
+    assert p.returncode == 0, p.stderr
+    lines = open(out).read().splitlines()
+    assert lines[0] == "# probe 32 32" and len(lines) == 1 + 32 * 32
+    s = R.BookScene("the_rest_of_your_life", overrides=dict(image_width=32))
+    ctx = R.Context(0)
+    gs = ctx.scene(s.desc)
+    ids, t = ctx.probe(gs, s.camera, 64)
+    got = np.array([ln.split()[0] for ln in lines[1:]], dtype=np.int32).reshape(32, 32)
+    assert np.array_equal(got, ids)
+    gs.close(); ctx.close()
+    bad = subprocess.run([RRT, "no_such_book"], capture_output=True, text=True, timeout=60)
+    assert bad.returncode == 1 and "books: in_one_weekend, the_next_week, the_rest_of_your_life" in bad.stderr
+    bad = subprocess.run([RRT, "--backend", "vulkan", "weekend"], capture_output=True, text=True, timeout=60)
+    assert bad.returncode == 2
