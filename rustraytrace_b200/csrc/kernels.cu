@@ -91,7 +91,7 @@ __device__ __forceinline__ void generate_ray(const DevScene& S, const DevCamera&
     P.ray.d = rel - lens;
   }
   P.ray.tm = 0.0f;
-  if (INTEGRATOR != RRT_INT_BOOK1 && S.has_motion) P.ray.tm = rng.draw(0xffffffffu, 1).x;  // camera.rs:169
+  if (INTEGRATOR != RRT_INT_BOOK1 && S.has_motion) P.ray.tm = r0.v;  // random_double() for the ray time, camera.rs:169
   P.T = V3f(1.0f, 1.0f, 1.0f); P.L = V3f(0.0f, 0.0f, 0.0f);
   P.bounce = 0; P.skip = -1;
 }
@@ -121,7 +121,7 @@ __device__ __forceinline__ bool shade_step(const DevScene& S, const DevCamera& C
       if (t2 > h.t) t2 = h.t;
       if (t1 >= t2) continue;
       if (t1 < 0.0f) t1 = 0.0f;
-      float xi = m == 0 ? ra.w : (m == 1 ? rb.x : (m == 2 ? rb.y : (m == 3 ? rb.z : rb.w)));
+      float xi = m == 0 ? ra.v : (m == 1 ? rb.x : (m == 2 ? rb.y : (m == 3 ? rb.z : rb.w)));
       float len = sqrtf(a);
       float inside = (t2 - t1) * len;
       float hit_distance = M.neg_inv_density * __logf(xi);
@@ -207,16 +207,20 @@ __device__ __forceinline__ bool shade_step(const DevScene& S, const DevCamera& C
   }
   if (pdf_branch) {
     // MixturePdf(HittablePdf(lights, p), srec.pdf), camera.rs:239-253, pdf.rs:77-100
-    const Rand4 rc = rng.draw((uint32_t)bounce, 2);
+    // one Philox block per bounce: ra.x is the mixture coin, and its remaining mantissa bits
+    // (2 ra.x mod 1, uniform and independent of the coin) pick the light; ra.y, ra.w give the
+    // direction; ra.z is the roulette draw above; ra.v the medium's free-flight draw
     const bool lamb = M.kind == RRT_M_LAMBERTIAN;
     const int nl = S.n_lights;
-    if (nl > 0 && ra.x < 0.5f) {
-      int li = min((int)(rc.x * (float)nl), nl - 1);  // random_int(0, n-1), hittable_list.rs:71-75
-      dir = light_random(S.lights[li], sf.p, rc.y, rc.z);
+    const bool pick_light = ra.x < 0.5f;
+    const float u_pick = 2.0f * ra.x - (pick_light ? 0.0f : 1.0f);
+    if (nl > 0 && pick_light) {
+      int li = min((int)(u_pick * (float)nl), nl - 1);  // random_int(0, n-1), hittable_list.rs:71-75
+      dir = light_random(S.lights[li], sf.p, ra.y, ra.w);
     } else if (lamb) {
-      dir = Onb(sf.n).transform(cosine_direction(rc.y, rc.z));  // pdf.rs:51-53
+      dir = Onb(sf.n).transform(cosine_direction(ra.y, ra.w));  // pdf.rs:51-53
     } else {
-      dir = uniform_sphere(rc.y, rc.z);  // SpherePdf, pdf.rs:27-29
+      dir = uniform_sphere(ra.y, ra.w);  // SpherePdf, pdf.rs:27-29
     }
     V3f udir = normalize(dir);
     float cos_n = dot(sf.n, udir);

@@ -9,7 +9,7 @@
 
 namespace rrt {
 
-struct Rand4 { float x, y, z, w; };
+struct Rand4 { float x, y, z, w, v; };  // v: a fifth uniform built from the low bytes u01 does not use
 
 __host__ __device__ inline void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
                                              uint32_t k0, uint32_t k1, uint32_t out[4]) {
@@ -39,6 +39,7 @@ struct PathRng {
     uint32_t o[4];
     philox4x32_10(pixel, sample, bounce, block, k0, k1, o);
     Rand4 r; r.x = u01(o[0]); r.y = u01(o[1]); r.z = u01(o[2]); r.w = u01(o[3]);
+    r.v = (float)(((o[0] & 255u) << 16) | ((o[1] & 255u) << 8) | (o[2] & 255u)) * (1.0f / 16777216.0f);
     return r;
   }
 };
