@@ -318,8 +318,18 @@ def main():
         paths_per_launch = my_paths / args.steps
         k_ms = kernel_ms / args.steps
         achieved = (paths_per_launch * f_path / (k_ms * 1e-3) / 1e12) if f_path else None
+        traffic, traffic_src = None, None
+        ncu_csv = os.path.join(ROOT, "profiles", "ncu_r01c_render_kernel_c2_spp64.csv")
+        if args.config == "C2" and os.path.exists(ncu_csv):   # the committed `ncu --set full` capture of this kernel
+            tot = 0.0
+            for ln in open(ncu_csv):
+                k, u, v = (ln.strip().split(",") + ["", ""])[:3]
+                if k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                    tot += float(v) * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u, 1)
+            traffic, traffic_src = int(tot), "profiles/ncu_r01c_render_kernel_c2_spp64.csv (64-spp launch; DRAM traffic is the frame, independent of spp)"
         roof = {"bound": "fp32", "achieved": round(achieved, 3) if achieved else None, "peak": round(peak_tf, 2),
-                "unit": "TFLOP/s", "frac": round(achieved / peak_tf, 4) if achieved else None, "traffic": None,
+                "unit": "TFLOP/s", "frac": round(achieved / peak_tf, 4) if achieved else None, "traffic": traffic, "traffic_source": traffic_src,
+                "algorithmic_dram_bytes": W * H * 16,
                 "kernel": "render_kernel", "kernel_ms": round(k_ms, 3), "flops_per_path": f_path,
                 "peak_source": f"{sm_count} SMs x 128 lanes x 2 x sm_max_mhz {sm_max:.0f} ({peak_src} MEASURED_PEAKS.json); "
                                "path tracing is FP32-pipe/latency bound, neither HBM nor tensor",
