@@ -163,6 +163,8 @@ def main():
     ap.add_argument("--no-e2e", action="store_true", help="skip the e2e leg (profiling runs)")
     args = ap.parse_args()
     rank, local_rank, world = env_int("RANK", 0), env_int("LOCAL_RANK", 0), env_int("WORLD_SIZE", 1)
+    if args.impl != "reference" and args.gpus != world:
+        print(f"bench.py: --gpus {args.gpus} but WORLD_SIZE={world}; launch with torch.distributed.run for N>1 (using {world})", file=sys.stderr)
     if args.impl == "reference":
         return run_reference(args, rank, world)
     args.warmup = max(3, args.warmup) if args.spp == 0 else args.warmup
