@@ -468,10 +468,12 @@ extern "C" int rrt_flatten_check(const rrt_scene_desc* desc, int32_t* n_prims, i
       if (it.node < 0 || it.node >= nn) return fail(RRT_ERR_INVALID, "flatten check: node index out of range");
       if (node_seen[it.node]++) return fail(RRT_ERR_INVALID, "flatten check: node reached twice");
       const float4* n = &F.nodes[4 * it.node];
-      Box c0 = {{(double)n[0].x - n[0].y, (double)n[0].z - n[0].w, (double)n[2].x - n[2].y},
-                {(double)n[0].x + n[0].y, (double)n[0].z + n[0].w, (double)n[2].x + n[2].y}};
-      Box c1 = {{(double)n[1].x - n[1].y, (double)n[1].z - n[1].w, (double)n[2].z - n[2].w},
-                {(double)n[1].x + n[1].y, (double)n[1].z + n[1].w, (double)n[2].z + n[2].w}};
+      const float* f = reinterpret_cast<const float*>(n);  // device_types.h: f[2a+k] centre, f[6+2a+k] half-extent
+      Box c0, c1;
+      for (int a = 0; a < 3; ++a) {
+        c0.lo[a] = (double)f[2 * a] - f[6 + 2 * a];         c0.hi[a] = (double)f[2 * a] + f[6 + 2 * a];
+        c1.lo[a] = (double)f[2 * a + 1] - f[6 + 2 * a + 1]; c1.hi[a] = (double)f[2 * a + 1] + f[6 + 2 * a + 1];
+      }
       if (it.has_box && (!inside(c0, it.box) || !inside(c1, it.box)))
         return fail(RRT_ERR_INVALID, "flatten check: child box escapes its parent");
       int refs[2] = {as_int(n[3].x), as_int(n[3].y)};

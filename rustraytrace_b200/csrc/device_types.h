@@ -35,8 +35,10 @@ enum PrimFlags { PF_UV_ROTATED = 1 };
 // ---- BVH inner node (float4 n[4]) ------------------------------------------------------------
 // boxes are (center c, half-extent e): the slab planes are c*(1/d) - o*(1/d) -+ e*|1/d|, three FMAs
 // per axis and no min/max pairs (the ALU pipe, not the FMA pipe, was the busy one: profiles/).
-// n0 = (c0.c.x, c0.e.x, c0.c.y, c0.e.y)   n1 = (c1.c.x, c1.e.x, c1.c.y, c1.e.y)
-// n2 = (c0.c.z, c0.e.z, c1.c.z, c1.e.z)   n3 = (ref0, ref1, 0, 0) as int bits
+// The two children sit side by side in every 64-bit pair so one packed FMA (fma.rn.f32x2, SASS
+// FFMA2) serves both: as 12 floats, f[2*axis + child] = centre, f[6 + 2*axis + child] = half-extent.
+// n0 = (c0.c.x, c1.c.x, c0.c.y, c1.c.y)   n1 = (c0.c.z, c1.c.z, c0.e.x, c1.e.x)
+// n2 = (c0.e.y, c1.e.y, c0.e.z, c1.e.z)   n3 = (ref0, ref1, 0, 0) as int bits
 // ref >= 0: inner node index.  ref < 0: leaf, ~ref = (first << 8) | (n_spheres << 4) | n_quads.
 static const int LEAF_MAX_PER_KIND = 15;
 inline
@@ -44,6 +46,16 @@ inline
 __host__ __device__
 #endif
 int make_leaf_ref(int first, int nsph, int nquad) { return ~((first << 8) | (nsph << 4) | nquad); }
+
+// accessors for the host flattener, the flatten check and the f64 probe (the render kernel reads pairs)
+inline
+#if defined(__CUDACC__)
+__host__ __device__
+#endif
+void node_set_child(float4* n, int child, const float c[3], const float e[3]) {
+  float* f = reinterpret_cast<float*>(n);
+  for (int a = 0; a < 3; ++a) { f[2 * a + child] = c[a]; f[6 + 2 * a + child] = e[a]; }
+}
 
 struct DevMaterial {  // 32 B
   int kind;           // rrt_material_kind

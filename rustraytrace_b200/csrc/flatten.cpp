@@ -686,10 +686,9 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
     box32(l.lo, l.hi, lc, lh); box32(r.lo, r.hi, rc, rh);
     int ref0 = l.left >= 0 ? inner_index[B.nodes[n].left] : leaf_ref[B.nodes[n].left];
     int ref1 = r.left >= 0 ? inner_index[B.nodes[n].right] : leaf_ref[B.nodes[n].right];
-    float4 a; a.x = lc[0]; a.y = lh[0]; a.z = lc[1]; a.w = lh[1];
-    float4 b; b.x = rc[0]; b.y = rh[0]; b.z = rc[1]; b.w = rh[1];
-    float4 c; c.x = lc[2]; c.y = lh[2]; c.z = rc[2]; c.w = rh[2];
-    out.nodes.push_back(a); out.nodes.push_back(b); out.nodes.push_back(c);
+    float4 rec[3];
+    node_set_child(rec, 0, lc, lh); node_set_child(rec, 1, rc, rh);
+    out.nodes.push_back(rec[0]); out.nodes.push_back(rec[1]); out.nodes.push_back(rec[2]);
     out.nodes.push_back(i4(ref0, ref1, 0, 0));
   }
   out.root_ref = 0;

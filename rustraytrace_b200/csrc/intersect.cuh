@@ -122,19 +122,41 @@ __device__ inline float safe_rcp(float d) {
   return 1.0f / (ad > 1e-30f ? d : copysignf(1e-30f, d));
 }
 
+// Packed FP32 FMA (Blackwell fma.rn.f32x2 -> SASS FFMA2): both halves of a 64-bit register pair in
+// one issue slot; ptxas folds negation, |x| and a scalar broadcast into the operand modifiers.
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) {
+  unsigned long long ra, rb, rc, rd;
+  ra = *reinterpret_cast<unsigned long long*>(&a);
+  rb = *reinterpret_cast<unsigned long long*>(&b);
+  rc = *reinterpret_cast<unsigned long long*>(&c);
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(ra), "l"(rb), "l"(rc));
+  return *reinterpret_cast<float2*>(&rd);
+}
+__device__ __forceinline__ float2 bcast2(float v) { return make_float2(v, v); }
+// sign flips as plain (non-.ftz) PTX so that ptxas can fold them into operand modifiers even under
+// --use_fast_math, whose neg.ftz/abs.ftz must flush denormals and so cost an instruction each
+__device__ __forceinline__ float neg_nf(float v) { float r; asm("neg.f32 %0, %1;" : "=f"(r) : "f"(v)); return r; }
+__device__ __forceinline__ float abs_nf(float v) { float r; asm("abs.f32 %0, %1;" : "=f"(r) : "f"(v)); return r; }
+__device__ __forceinline__ float2 neg2(float2 v) { return make_float2(neg_nf(v.x), neg_nf(v.y)); }
+
 // Aabb::hit (aabb.rs:52-84) for both children of a node.  Boxes are (center, half-extent), so the
-// two plane distances of an axis are tc -+ e*|1/d| with tc = c*(1/d) - o*(1/d): 3 FMAs per axis and
-// child, then one 3-input max/min per interval end — no per-axis min/max pairs.
+// two plane distances of an axis are tc -+ e*|1/d| with tc = c*(1/d) - o*(1/d); every pair of the
+// node record is (child0, child1) (device_types.h), so that is 9 packed FMAs for both children,
+// then one 3-input max/min per interval end — no per-axis min/max pairs.
 __device__ __forceinline__ void slab2(float4 n0, float4 n1, float4 n2, float idx, float idy, float idz,
                                       float oodx, float oody, float oodz, float tmin, float tmax,
                                       float& near0, float& far0, float& near1, float& far1) {
-  const float ax = fabsf(idx), ay = fabsf(idy), az = fabsf(idz);
-  const float t0x = fmaf(n0.x, idx, -oodx), t0y = fmaf(n0.z, idy, -oody), t0z = fmaf(n2.x, idz, -oodz);
-  const float t1x = fmaf(n1.x, idx, -oodx), t1y = fmaf(n1.z, idy, -oody), t1z = fmaf(n2.z, idz, -oodz);
-  near0 = fmaxf(fmaxf(fmaf(-n0.y, ax, t0x), fmaf(-n0.w, ay, t0y)), fmaxf(fmaf(-n2.y, az, t0z), tmin));
-  far0 = fminf(fminf(fmaf(n0.y, ax, t0x), fmaf(n0.w, ay, t0y)), fminf(fmaf(n2.y, az, t0z), tmax));
-  near1 = fmaxf(fmaxf(fmaf(-n1.y, ax, t1x), fmaf(-n1.w, ay, t1y)), fmaxf(fmaf(-n2.w, az, t1z), tmin));
-  far1 = fminf(fminf(fmaf(n1.y, ax, t1x), fmaf(n1.w, ay, t1y)), fminf(fmaf(n2.w, az, t1z), tmax));
+  const float2 tx = fma2(make_float2(n0.x, n0.y), bcast2(idx), bcast2(neg_nf(oodx)));
+  const float2 ty = fma2(make_float2(n0.z, n0.w), bcast2(idy), bcast2(neg_nf(oody)));
+  const float2 tz = fma2(make_float2(n1.x, n1.y), bcast2(idz), bcast2(neg_nf(oodz)));
+  const float2 ex = make_float2(n1.z, n1.w), ey = make_float2(n2.x, n2.y), ez = make_float2(n2.z, n2.w);
+  const float2 ax = bcast2(abs_nf(idx)), ay = bcast2(abs_nf(idy)), az = bcast2(abs_nf(idz));
+  const float2 fx = fma2(ex, ax, tx), fy = fma2(ey, ay, ty), fz = fma2(ez, az, tz);
+  const float2 nx = fma2(neg2(ex), ax, tx), ny = fma2(neg2(ey), ay, ty), nz = fma2(neg2(ez), az, tz);
+  near0 = fmaxf(fmaxf(nx.x, ny.x), fmaxf(nz.x, tmin));
+  far0 = fminf(fminf(fx.x, fy.x), fminf(fz.x, tmax));
+  near1 = fmaxf(fmaxf(nx.y, ny.y), fmaxf(nz.y, tmin));
+  far1 = fminf(fminf(fx.y, fy.y), fminf(fz.y, tmax));
 }
 
 // World::hit for the render kernel: closest hit in (tmin, +inf).
@@ -301,12 +323,14 @@ __device__ inline void world_hit64(const DevScene& S, V3d o, V3d d, double tmin,
       const float4* g = S.nodes + 4 * cur;
       float4 n0 = ldg4(g), n1 = ldg4(g + 1), n2 = ldg4(g + 2), n3 = ldg4(g + 3);
       // (center, half-extent) -> planes; the boxes are conservative supersets of the reference's
-      double c0x0 = ((double)n0.x - (double)n0.y - o.x) * idx, c0x1 = ((double)n0.x + (double)n0.y - o.x) * idx;
-      double c0y0 = ((double)n0.z - (double)n0.w - o.y) * idy, c0y1 = ((double)n0.z + (double)n0.w - o.y) * idy;
-      double c0z0 = ((double)n2.x - (double)n2.y - o.z) * idz, c0z1 = ((double)n2.x + (double)n2.y - o.z) * idz;
-      double c1x0 = ((double)n1.x - (double)n1.y - o.x) * idx, c1x1 = ((double)n1.x + (double)n1.y - o.x) * idx;
-      double c1y0 = ((double)n1.z - (double)n1.w - o.y) * idy, c1y1 = ((double)n1.z + (double)n1.w - o.y) * idy;
-      double c1z0 = ((double)n2.z - (double)n2.w - o.z) * idz, c1z1 = ((double)n2.z + (double)n2.w - o.z) * idz;
+      const double cx0 = n0.x, cx1 = n0.y, cy0 = n0.z, cy1 = n0.w, cz0 = n1.x, cz1 = n1.y;
+      const double ex0 = n1.z, ex1 = n1.w, ey0 = n2.x, ey1 = n2.y, ez0 = n2.z, ez1 = n2.w;
+      double c0x0 = (cx0 - ex0 - o.x) * idx, c0x1 = (cx0 + ex0 - o.x) * idx;
+      double c0y0 = (cy0 - ey0 - o.y) * idy, c0y1 = (cy0 + ey0 - o.y) * idy;
+      double c0z0 = (cz0 - ez0 - o.z) * idz, c0z1 = (cz0 + ez0 - o.z) * idz;
+      double c1x0 = (cx1 - ex1 - o.x) * idx, c1x1 = (cx1 + ex1 - o.x) * idx;
+      double c1y0 = (cy1 - ey1 - o.y) * idy, c1y1 = (cy1 + ey1 - o.y) * idy;
+      double c1z0 = (cz1 - ez1 - o.z) * idz, c1z1 = (cz1 + ez1 - o.z) * idz;
       double near0 = fmax(fmax(fmin(c0x0, c0x1), fmin(c0y0, c0y1)), fmax(fmin(c0z0, c0z1), tmin));
       double far0 = fmin(fmin(fmax(c0x0, c0x1), fmax(c0y0, c0y1)), fmin(fmax(c0z0, c0z1), h.t));
       double near1 = fmax(fmax(fmin(c1x0, c1x1), fmin(c1y0, c1y1)), fmax(fmin(c1z0, c1z1), tmin));
