@@ -171,20 +171,22 @@ __device__ inline void world_hit32(const DevScene& S, const Ray32& r, float tmin
     return;
   }
   const float idx = safe_rcp(r.d.x), idy = safe_rcp(r.d.y), idz = safe_rcp(r.d.z);
-  const float oodx = r.o.x * idx, oody = r.o.y * idy, oodz = r.o.z * idz;
+  float oodx = r.o.x * idx, oody = r.o.y * idy, oodz = r.o.z * idz;
+  asm("" : "+f"(oodx), "+f"(oody), "+f"(oodz));  // opaque: keep in registers, do not rematerialise in the loop
   int stack[RRT_STACK];
   int sp = 0;
   // while-while traversal (Aila & Laine 2009): every lane first descends through inner nodes until
   // it holds a leaf, then the warp reconverges and processes leaves together; the single mixed
   // loop this replaces ran the inner-node and the leaf body serially whenever lanes disagreed
-  // (warp execution efficiency 42 % in profiles/ncu_r01_*).  Measured alternatives that lost: a lane
+  // (warp execution efficiency 42 % in profiles/ncu_r01_*).  Measured alternatives that lost: postponing
+  // a found leaf and descending speculatively to the next one (-25 %, wasted node visits), a lane
   // state machine voting on the next step every iteration (+35 % time, vote overhead), and leaving
   // this inner loop early once fewer than N lanes are still descending (+4 % for every N).
   for (;;) {
     bool done = false;
     while (cur >= 0) {
       float4 n0, n1, n2, n3;
-      const float4* g = S.nodes + 4 * cur;
+      const float4* g = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(S.nodes) + (size_t)(unsigned)cur * 64u);
       n0 = ldg4(g); n1 = ldg4(g + 1); n2 = ldg4(g + 2); n3 = ldg4(g + 3);
       float near0, far0, near1, far1;
       slab2(n0, n1, n2, idx, idy, idz, oodx, oody, oodz, tmin, h.t, near0, far0, near1, far1);
@@ -212,7 +214,6 @@ __device__ inline void world_hit32(const DevScene& S, const Ray32& r, float tmin
     }
   }
 }
-
 // Closest hit of a medium boundary run in [lo, hi] for quads / (lo, hi) for spheres
 // (boundary.hit(r, interval), constant_medium.rs:41-42).  Returns t or -1 flagged by `found`.
 __device__ inline bool boundary_hit32(const float4* __restrict__ bprims, const DevMedium& m, const Ray32& r,
