@@ -321,14 +321,16 @@ def main():
         k_ms = kernel_ms / args.steps
         achieved = (paths_per_launch * f_path / (k_ms * 1e-3) / 1e12) if f_path else None
         traffic, traffic_src = None, None
-        ncu_csv = os.path.join(ROOT, "profiles", "ncu_r01c_render_kernel_c2_spp64.csv")
-        if args.config == "C2" and os.path.exists(ncu_csv):   # the committed `ncu --set full` capture of this kernel
+        import glob
+        caps = sorted(glob.glob(os.path.join(ROOT, "profiles", "ncu_r*_render_kernel_c2_spp64.csv")))
+        ncu_csv = caps[-1] if caps else ""   # the newest capture (names sort by round)
+        if args.config == "C2" and ncu_csv:   # the committed `ncu --set full` capture of this kernel
             tot = 0.0
             for ln in open(ncu_csv):
                 k, u, v = (ln.strip().split(",") + ["", ""])[:3]
                 if k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
                     tot += float(v) * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u, 1)
-            traffic, traffic_src = int(tot), "profiles/ncu_r01c_render_kernel_c2_spp64.csv (64-spp launch; DRAM traffic is the frame, independent of spp)"
+            traffic, traffic_src = int(tot), "profiles/" + os.path.basename(ncu_csv) + " (64-spp launch; DRAM traffic is the frame, independent of spp)"
         roof = {"bound": "fp32", "achieved": round(achieved, 3) if achieved else None, "peak": round(peak_tf, 2),
                 "unit": "TFLOP/s", "frac": round(achieved / peak_tf, 4) if achieved else None, "traffic": traffic, "traffic_source": traffic_src,
                 "algorithmic_dram_bytes": W * H * 16,
