@@ -17,6 +17,9 @@ all: $(PKG)/librrt.so $(PKG)/librrt_host.so $(PKG)/bin/rrt oracle
 
 $(CSRC)/kernels.o: $(CSRC)/kernels.cu $(CSRC)/*.cuh $(CSRC)/*.h include/rrt.h
 	$(NVCC) $(NVFLAGS) -c $< -o $@
+# render_kernel<INTEGRATOR, FEAT> instances, one translation unit per book so they build in parallel
+$(CSRC)/kernels_book%.o: $(CSRC)/kernels_book%.cu $(CSRC)/*.cuh $(CSRC)/*.h include/rrt.h
+	$(NVCC) $(NVFLAGS) -c $< -o $@
 $(CSRC)/probe64.o: $(CSRC)/probe64.cu $(CSRC)/*.cuh $(CSRC)/*.h include/rrt.h
 	$(NVCC) -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -fmad=false -Xcompiler -fPIC -c $< -o $@
 $(CSRC)/api.o: $(CSRC)/api.cu $(CSRC)/*.cuh $(CSRC)/*.h $(CSRC)/flatten.hpp include/rrt.h
@@ -24,7 +27,8 @@ $(CSRC)/api.o: $(CSRC)/api.cu $(CSRC)/*.cuh $(CSRC)/*.h $(CSRC)/flatten.hpp incl
 $(CSRC)/flatten.o: $(CSRC)/flatten.cpp $(CSRC)/flatten.hpp $(CSRC)/device_types.h include/rrt.h
 	$(NVCC) $(NVFLAGS) -x cu -c $< -o $@
 
-$(PKG)/librrt.so: $(CSRC)/kernels.o $(CSRC)/probe64.o $(CSRC)/api.o $(CSRC)/flatten.o
+KOBJ := $(CSRC)/kernels_book1.o $(CSRC)/kernels_book2.o $(CSRC)/kernels_book3.o
+$(PKG)/librrt.so: $(CSRC)/kernels.o $(KOBJ) $(CSRC)/probe64.o $(CSRC)/api.o $(CSRC)/flatten.o
 	$(NVCC) -shared -o $@ $^ -cudart shared
 
 HOST_SRC := $(HOST)/books.cpp $(HOST)/rtw_image.cpp $(HOST)/jpeg_decode.cpp $(HOST)/render_io.cpp

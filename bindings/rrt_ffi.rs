@@ -30,7 +30,7 @@ pub struct RrtRenderParams { pub integrator: i32, pub shard_mode: i32, pub rank:
 #[repr(C)] #[derive(Clone, Copy, Default)]
 pub struct RrtStats { pub width: i32, pub height: i32, pub spp_effective: i32, pub kernel_launches: i32,
                       pub paths: f64, pub kernel_ms: f64, pub total_ms: f64, pub h2d_bytes: u64, pub d2h_bytes: u64,
-                      pub n_prims: i32, pub n_bvh_nodes: i32, pub n_media: i32, pub n_lights: i32, pub sm_count: i32, pub _pad: i32 }
+                      pub n_prims: i32, pub n_bvh_nodes: i32, pub n_media: i32, pub n_lights: i32, pub sm_count: i32, pub kernel_features: i32 }
 #[repr(C)] pub struct RrtCtx { _p: [u8; 0] }
 #[repr(C)] pub struct RrtScene { _p: [u8; 0] }
 
@@ -52,6 +52,7 @@ extern "C" {
                           n_super_tiles: *mut i32, n_pixels: *mut f64, owner_mask: *mut u8) -> c_int;
     pub fn rrt_flatten_check(desc: *const RrtSceneDesc, n_prims: *mut i32, n_nodes: *mut i32, bvh_depth: *mut i32,
                              n_media: *mut i32, n_lights: *mut i32) -> c_int;
+    pub fn rrt_scene_features(desc: *const RrtSceneDesc, features: *mut i32) -> c_int;
     pub fn rrt_philox_kat(c0: u32, c1: u32, c2: u32, c3: u32, k0: u32, k1: u32, out4: *mut u32);
     pub fn rrt_version() -> *const c_char;
     pub fn rrt_last_error() -> *const c_char;

@@ -167,7 +167,10 @@ typedef struct rrt_stats {
   uint64_t h2d_bytes, d2h_bytes;
   int32_t n_prims, n_bvh_nodes, n_media, n_lights;
   int32_t sm_count;
-  int32_t _pad;
+  int32_t kernel_features; /* feature set of the render-kernel instance the last call ran: bit 0 moving
+                            * spheres, 1 quads, 2 constant media, 3 non-solid textures (15 = the
+                            * general instance); a scene runs on the smallest instance covering it.
+                            * RRT_KERNEL=full in the environment at rrt_init forces 15 (debugging). */
 } rrt_stats;
 
 typedef struct rrt_ctx rrt_ctx;
@@ -232,9 +235,12 @@ int rrt_shard_plan(const rrt_camera* cam, const rrt_render_params* params, int32
 /* Host-only hooks (no GPU needed; used by the CPU test tier):
  *   rrt_flatten_check: runs the flattener + BVH build on the host and verifies the result (every
  *   primitive in exactly one leaf, every child box inside its parent's).  Outputs may be NULL.
+ *   rrt_scene_features: the feature bits the flattened scene needs (rrt_stats.kernel_features lists
+ *   them); the render calls pick the smallest kernel instance that covers them.
  *   rrt_philox_kat:    one Philox4x32-10 block (the sampling RNG), for known-answer tests. */
 int rrt_flatten_check(const rrt_scene_desc* desc, int32_t* n_prims, int32_t* n_nodes, int32_t* bvh_depth,
                       int32_t* n_media, int32_t* n_lights);
+int rrt_scene_features(const rrt_scene_desc* desc, int32_t* features);
 void rrt_philox_kat(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1,
                     uint32_t* out4);
 const char* rrt_last_error(void);

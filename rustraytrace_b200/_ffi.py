@@ -68,7 +68,7 @@ class Stats(C.Structure):
                 ("paths", c_dbl), ("kernel_ms", c_dbl), ("total_ms", c_dbl),
                 ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
                 ("n_prims", c_int), ("n_bvh_nodes", c_int), ("n_media", c_int), ("n_lights", c_int),
-                ("sm_count", c_int), ("_pad", c_int)]
+                ("sm_count", c_int), ("kernel_features", c_int)]
 
 
 class Overrides(C.Structure):
@@ -83,6 +83,7 @@ M_LAMBERTIAN, M_METAL, M_DIELECTRIC, M_DIFFUSE_LIGHT, M_ISOTROPIC, M_EMPTY = ran
 T_SOLID, T_CHECKER, T_IMAGE, T_NOISE = range(4)
 INT_BOOK1, INT_BOOK2, INT_BOOK3 = 1, 2, 3
 SHARD_NONE, SHARD_TILE, SHARD_SAMPLE = 0, 1, 2
+SF_MOTION, SF_QUADS, SF_MEDIA, SF_TEXTURES, SF_ALL = 1, 2, 4, 8, 15  # rrt_stats.kernel_features bits
 BOOK_1, BOOK_2, BOOK_3, BOOK_1_GPU = 1, 2, 3, 4
 OK, ERR_INVALID, ERR_CUDA, ERR_UNSUPPORTED, ERR_NO_DEVICE = 0, -1, -2, -3, -4
 O_BITS = {"aspect_ratio": 1 << 0, "image_width": 1 << 1, "samples_per_pixel": 1 << 2, "max_depth": 1 << 3,
@@ -108,6 +109,7 @@ RRT_SYMBOLS = [
     ("rrt_shard_plan", c_int, [C.POINTER(Camera), C.POINTER(RenderParams), C.POINTER(c_int), C.POINTER(c_int),
                                C.POINTER(c_int), C.POINTER(c_dbl), VP]),
     ("rrt_flatten_check", c_int, [C.POINTER(SceneDesc)] + [C.POINTER(c_int)] * 5),
+    ("rrt_scene_features", c_int, [C.POINTER(SceneDesc), C.POINTER(c_int)]),
     ("rrt_philox_kat", None, [C.c_uint32] * 6 + [C.POINTER(C.c_uint32)]),
     ("rrt_last_error", C.c_char_p, []),
     ("rrt_version", C.c_char_p, []),

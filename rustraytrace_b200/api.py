@@ -201,6 +201,13 @@ def flatten_check(desc):
     return dict(zip(("n_prims", "n_nodes", "bvh_depth", "n_media", "n_lights"), [x.value for x in v]))
 
 
+def scene_features(desc):
+    """Host-only: SF_* feature bits of the flattened scene (which render-kernel instance it runs on)."""
+    v = F.c_int()
+    _check(F.rrt().rrt_scene_features(C.byref(desc), C.byref(v)))
+    return v.value
+
+
 def shard_plan(camera, integrator, shard_mode, rank, world, mask=False):
     """rrt_shard_plan (host only): this rank's sample range / tiles / pixel count [/ owner mask]."""
     p = F.RenderParams(int(integrator), int(shard_mode), int(rank), int(world), 0)

@@ -40,6 +40,7 @@ struct rrt_ctx {
   float* accum = nullptr;  // grow-only frame buffer for the host-output entry points
   size_t accum_floats = 0;
   rrt_stats stats;
+  bool force_full_kernel = false;     // RRT_KERNEL=full: always run the SF_ALL render kernel instance (include/rrt.h)
   std::vector<rrt_scene*> scenes;  // live scenes of this context (released by rrt_shutdown if the caller did not)
 };
 
@@ -93,6 +94,8 @@ int rrt_init(int device, rrt_ctx** out) {
     return fail(RRT_ERR_NO_DEVICE, std::string("device '") + prop.name + "' is not sm_100-class; kernels are built for sm_100a only");
   }
   c->sm_count = prop.multiProcessorCount;
+  const char* kv = std::getenv("RRT_KERNEL");
+  c->force_full_kernel = kv && std::strcmp(kv, "full") == 0;
   CK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking), "cudaStreamCreate");
   c->stream = c->own_stream;
   for (auto& ev : c->ev) CK(cudaEventCreate(&ev), "cudaEventCreate");
@@ -175,6 +178,7 @@ int rrt_scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out) {
   D.n_media = (int)F.media.size();
   D.n_lights = (int)F.lights.size();
   D.has_motion = F.has_motion;
+  D.features = F.features;
   if (D.n_media > 5) { rrt_scene_destroy(sc); return fail(RRT_ERR_UNSUPPORTED, "more than 5 constant media"); }
   sc->n_nodes = D.n_nodes; sc->n_prims = D.n_prims; sc->n_media = D.n_media; sc->n_lights = D.n_lights;
   cudaError_t e = cudaStreamSynchronize(c->stream);  // host vectors die at return
@@ -257,7 +261,8 @@ int rrt_render_device(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, co
   const int Wd = W.width, H = W.height, spp_eff = W.spp_eff;
   const int n_samples = W.s_end - W.s_begin;
 
-  int bps = render_blocks_per_sm(p->integrator);
+  const RenderVariant* variant = select_render_variant(p->integrator, sc->dev.features, c->force_full_kernel);
+  int bps = render_blocks_per_sm(variant);
   if (bps < 1) return fail(RRT_ERR_CUDA, "kernel launch failed: render kernel does not fit on an SM");
   const int grid = c->sm_count * bps;
   const long long resident_warps = (long long)grid * (RRT_BLOCK / 32);
@@ -279,7 +284,7 @@ int rrt_render_device(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, co
   int launches = 0;
   CK(cudaEventRecord(c->ev[1], c->stream), "cudaEventRecord");
   if (W.n_tiles > 0 && n_samples > 0) {
-    CK(launch_render(A, grid, c->stream), "kernel launch failed");
+    CK(launch_render(variant, A, grid, c->stream), "kernel launch failed");
     launches = 1;
   }
   CK(cudaEventRecord(c->ev[2], c->stream), "cudaEventRecord");
@@ -295,6 +300,7 @@ int rrt_render_device(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, co
   st.d2h_bytes = 0;
   st.n_prims = sc->n_prims; st.n_bvh_nodes = sc->n_nodes; st.n_media = sc->n_media; st.n_lights = sc->n_lights;
   st.sm_count = c->sm_count;
+  st.kernel_features = launches ? variant->features : -1;
   return RRT_OK;
 }
 
@@ -440,6 +446,16 @@ bool inside(const Box& c, const Box& p) {
 }
 int as_int(float f) { int i; std::memcpy(&i, &f, 4); return i; }
 }  // namespace
+
+extern "C" int rrt_scene_features(const rrt_scene_desc* desc, int32_t* features) {
+  if (!features) return fail(RRT_ERR_INVALID, "rrt_scene_features: features is null");
+  FlatScene F;
+  std::string err;
+  int st = flatten_scene(desc, F, err);
+  if (st != RRT_OK) return fail(st, err);
+  *features = F.features;
+  return RRT_OK;
+}
 
 extern "C" int rrt_flatten_check(const rrt_scene_desc* desc, int32_t* n_prims, int32_t* n_nodes, int32_t* bvh_depth,
                                  int32_t* n_media, int32_t* n_lights) {

@@ -57,6 +57,17 @@ void node_set_child(float4* n, int child, const float c[3], const float e[3]) {
   for (int a = 0; a < 3; ++a) { f[2 * a + child] = c[a]; f[6 + 2 * a + child] = e[a]; }
 }
 
+// ---- scene features ------------------------------------------------------------------------------
+// What a flattened scene needs from the render kernel.  render_kernel<INTEGRATOR, FEAT> is compiled
+// for a few feature sets and a scene runs on the smallest one covering it (kernels.cu).
+enum SceneFeature {
+  SF_MOTION = 1,    // a sphere with center1 != center0 (ray time, sphere.rs:70)
+  SF_QUADS = 2,     // quads in the BVH
+  SF_MEDIA = 4,     // constant media
+  SF_TEXTURES = 8,  // a material whose texture is not a solid colour (checker / image / noise)
+  SF_ALL = 15
+};
+
 struct DevMaterial {  // 32 B
   int kind;           // rrt_material_kind
   int tex;            // texture index or -1
@@ -134,6 +145,7 @@ struct DevScene {
   int root_ref;
   int n_nodes, n_prims, n_media, n_lights;
   int has_motion;    // any sphere with dc != 0
+  int features;      // SceneFeature bits
 };
 
 // One launch's share of the frame.

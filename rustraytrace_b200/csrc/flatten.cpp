@@ -633,6 +633,10 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
   out.n_prims = (int)P.size();
   for (const BakedPrim& p : P) if (p.kind == PRIM_SPHERE && (p.dc.x != 0 || p.dc.y != 0 || p.dc.z != 0)) out.has_motion = 1;
   for (const BakedPrim& p : w.boundary) if (p.kind == PRIM_SPHERE && (p.dc.x != 0 || p.dc.y != 0 || p.dc.z != 0)) out.has_motion = 1;
+  if (out.has_motion) out.features |= SF_MOTION;
+  for (const BakedPrim& p : P) if (p.kind != PRIM_SPHERE) out.features |= SF_QUADS;
+  if (!out.media.empty()) out.features |= SF_MEDIA;
+  for (const DevMaterial& m : out.materials) if (m.tex >= 0) out.features |= SF_TEXTURES;  // solid colours were folded into albedo
   if (P.empty()) { out.root_ref = make_leaf_ref(0, 0, 0); return RRT_OK; }
   int ns = 0, nq = 0;
   for (const BakedPrim& p : P) (p.kind == PRIM_SPHERE ? ns : nq)++;

@@ -26,6 +26,7 @@ struct FlatScene {
   int root_ref = -1;
   int n_prims = 0;
   int has_motion = 0;
+  int features = 0;   // SceneFeature bits (device_types.h): which render kernel instance the scene needs
   int bvh_depth = 0;
 };
 

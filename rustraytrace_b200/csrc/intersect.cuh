@@ -107,12 +107,14 @@ __device__ inline void quad_hit32(const float4* __restrict__ prims, int i, const
 }
 
 // One leaf: a contiguous run, spheres first.  ~ref = (first << 8) | (nsph << 4) | nquad.
+template <int FEAT>
 __device__ inline void leaf_hit32(const float4* __restrict__ prims, int leaf, const Ray32& r, float a,
                                   float inv_a, float tmin, int skip, bool motion, Hit32& h) {
   int first = leaf >> 8, ns = (leaf >> 4) & 15, nq = leaf & 15;
   for (int k = 0; k < ns; ++k) sphere_hit32(prims, first + k, r, a, inv_a, tmin, skip, motion, h);
   first += ns;
-  for (int k = 0; k < nq; ++k) quad_hit32(prims, first + k, r, tmin, skip, h);
+  if (FEAT & SF_QUADS)
+    for (int k = 0; k < nq; ++k) quad_hit32(prims, first + k, r, tmin, skip, h);
 }
 
 __device__ inline float safe_rcp(float d) {
@@ -161,13 +163,14 @@ __device__ __forceinline__ void slab2(float4 n0, float4 n1, float4 n2, float idx
 
 // World::hit for the render kernel: closest hit in (tmin, +inf).
 // Nodes and primitives come through L1 (ld.global.nc).
+template <int FEAT>
 __device__ inline void world_hit32(const DevScene& S, const Ray32& r, float tmin, int skip, Hit32& h) {
   const float a = dot(r.d, r.d);
   const float inv_a = 1.0f / a;
-  const bool motion = S.has_motion != 0;
+  const bool motion = (FEAT & SF_MOTION) && S.has_motion != 0;
   int cur = S.root_ref;
   if (cur < 0) {  // the whole scene is one leaf: brute force, uniform control flow
-    leaf_hit32(S.prims, ~cur, r, a, inv_a, tmin, skip, motion, h);
+    leaf_hit32<FEAT>(S.prims, ~cur, r, a, inv_a, tmin, skip, motion, h);
     return;
   }
   const float idx = safe_rcp(r.d.x), idy = safe_rcp(r.d.y), idz = safe_rcp(r.d.z);
@@ -208,7 +211,7 @@ __device__ inline void world_hit32(const DevScene& S, const Ray32& r, float tmin
     }
     if (done) break;
     if (cur < 0) {
-      leaf_hit32(S.prims, ~cur, r, a, inv_a, tmin, skip, motion, h);
+      leaf_hit32<FEAT>(S.prims, ~cur, r, a, inv_a, tmin, skip, motion, h);
       if (sp == 0) break;
       cur = stack[--sp];
     }

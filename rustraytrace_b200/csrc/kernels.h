@@ -5,9 +5,6 @@
 #include "device_types.h"
 
 #define RRT_BLOCK 128
-#ifndef RRT_MIN_BLOCKS
-#define RRT_MIN_BLOCKS 6  // 80 registers/thread, no spills; 24 warps per SM
-#endif
 
 namespace rrt {
 
@@ -28,8 +25,33 @@ struct ProbeArgs {
   double* t;
 };
 
-cudaError_t launch_render(const RenderArgs& A, int grid, cudaStream_t st);
-int render_blocks_per_sm(int integrator);
+// Resident CTAs per SM each render kernel instance is compiled for (its register budget).  Without
+// textures and moving spheres the kernel fits 64 registers spill-free: 8 CTAs, 32 warps per SM.
+// Perlin/image/checker lookups and the time-dependent sphere centre push it to 80 registers
+// (6 CTAs); 72 registers spill there and measured within 1 % (profiles/README.md).
+#ifndef RRT_MIN_BLOCKS_LEAN
+#define RRT_MIN_BLOCKS_LEAN 8
+#endif
+#ifndef RRT_MIN_BLOCKS
+#define RRT_MIN_BLOCKS 6
+#endif
+constexpr int render_min_blocks(int feat) {
+  return (feat & (SF_TEXTURES | SF_MOTION)) ? RRT_MIN_BLOCKS : RRT_MIN_BLOCKS_LEAN;
+}
+
+// One compiled instance of render_kernel<INTEGRATOR, FEAT> (kernels_book{1,2,3}.cu).
+struct RenderVariant {
+  int features;                 // SceneFeature bits the instance supports
+  void (*kernel)(RenderArgs);   // __global__ entry
+};
+const RenderVariant* render_variants_book1(int* n);
+const RenderVariant* render_variants_book2(int* n);
+const RenderVariant* render_variants_book3(int* n);
+
+// Smallest instance of the integrator covering `features` (force_full: the SF_ALL instance).
+const RenderVariant* select_render_variant(int integrator, int features, bool force_full);
+cudaError_t launch_render(const RenderVariant* v, const RenderArgs& A, int grid, cudaStream_t st);
+int render_blocks_per_sm(const RenderVariant* v);
 cudaError_t launch_probe(const ProbeArgs& A, int precision, cudaStream_t st);
 cudaError_t launch_probe64(const ProbeArgs& A, cudaStream_t st);  // probe64.cu (-fmad=false)
 cudaError_t launch_resolve(const float* accum, int n, int spp, unsigned char* rgb, cudaStream_t st);

@@ -1,0 +1,21 @@
+// kernels_book2.cu — render_kernel instances for the book-2 integrator, smallest feature set first
+// (select_render_variant takes the first that covers the scene).
+#include "render_kernel.cuh"
+
+namespace rrt {
+
+const RenderVariant* render_variants_book2(int* n) {
+  static const RenderVariant table[] = {
+    {0, render_kernel<RRT_INT_BOOK2, 0>},
+    {SF_TEXTURES, render_kernel<RRT_INT_BOOK2, SF_TEXTURES>},
+    {SF_MOTION | SF_TEXTURES, render_kernel<RRT_INT_BOOK2, SF_MOTION | SF_TEXTURES>},
+    {SF_QUADS, render_kernel<RRT_INT_BOOK2, SF_QUADS>},
+    {SF_QUADS | SF_TEXTURES, render_kernel<RRT_INT_BOOK2, SF_QUADS | SF_TEXTURES>},
+    {SF_QUADS | SF_MEDIA, render_kernel<RRT_INT_BOOK2, SF_QUADS | SF_MEDIA>},
+    {SF_ALL, render_kernel<RRT_INT_BOOK2, SF_ALL>},
+  };
+  *n = (int)(sizeof table / sizeof table[0]);
+  return table;
+}
+
+}  // namespace rrt

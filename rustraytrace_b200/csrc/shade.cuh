@@ -109,12 +109,13 @@ __device__ inline void sphere_uv(V3f n, float& u, float& v) {
 }
 
 // Rebuild the HitRecord of the closest primitive (sphere.rs:91-95, quad.rs:76-88).
+template <int FEAT>
 __device__ inline void make_surface(const DevScene& S, const Ray32& r, const Hit32& h, Surface& s) {
   int idx = h.prim & ~PRIM_QUAD_BIT;
   const float4* rec = S.prims + 4 * idx;
   V3f p = r.o + h.t * r.d;
   V3f outward;
-  if (h.prim & PRIM_QUAD_BIT) {
+  if ((FEAT & SF_QUADS) && (h.prim & PRIM_QUAD_BIT)) {
     float4 p0 = ldg4(rec), p1 = ldg4(rec + 1), p2 = ldg4(rec + 2), m = ldg4(rec + 3);
     outward = V3f(p0.x, p0.y, p0.z);
     s.u = dot(p, V3f(p1.x, p1.y, p1.z)) + p1.w;
@@ -126,7 +127,7 @@ __device__ inline void make_surface(const DevScene& S, const Ray32& r, const Hit
   } else {
     float4 p0 = ldg4(rec), p1 = ldg4(rec + 1), m = ldg4(rec + 2);
     V3f c(p0.x, p0.y, p0.z);
-    if (S.has_motion) c = c + r.tm * V3f(p1.x, p1.y, p1.z);
+    if ((FEAT & SF_MOTION) && S.has_motion) c = c + r.tm * V3f(p1.x, p1.y, p1.z);
     outward = (p - c) * p1.w;                       // (p - center) / radius
     outward = normalize(outward);
     p = c + p0.w * outward;                         // back onto the sphere

@@ -10,10 +10,11 @@ mkdir -p $out
 C=rustraytrace_b200/csrc
 F="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC"
 nvcc $F --use_fast_math "$@" -c $C/kernels.cu -o $tmp/kernels.o &
+for b in 1 2 3; do nvcc $F --use_fast_math "$@" -c $C/kernels_book$b.cu -o $tmp/kernels_book$b.o & done
 nvcc $F -fmad=false "$@" -c $C/probe64.cu -o $tmp/probe64.o &
 nvcc $F --use_fast_math "$@" -c $C/api.cu -o $tmp/api.o &
 nvcc $F --use_fast_math "$@" -x cu -c $C/flatten.cpp -o $tmp/flatten.o &
 wait
-nvcc -shared -o $out/librrt_$name.so $tmp/kernels.o $tmp/probe64.o $tmp/api.o $tmp/flatten.o -cudart shared 2>/dev/null
+nvcc -shared -o $out/librrt_$name.so $tmp/kernels.o $tmp/kernels_book1.o $tmp/kernels_book2.o $tmp/kernels_book3.o $tmp/probe64.o $tmp/api.o $tmp/flatten.o -cudart shared 
 rm -rf $tmp
 echo built $out/librrt_$name.so

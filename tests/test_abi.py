@@ -84,6 +84,22 @@ def test_flattener_self_check_on_every_book_scene(book, scene_no):
         assert c["n_prims"] == 13 and c["n_lights"] == 2
 
 
+def test_scene_feature_bits_select_the_kernel_instance():
+    """rrt_scene_features: which render_kernel<INTEGRATOR, FEAT> instance a scene needs (csrc/kernels.h)."""
+    def feat(book, no=None):
+        s = R.BookScene(book, no, overrides=dict(image_width=64))
+        return R.scene_features(s.desc)
+    assert feat("in_one_weekend") == 0                      # static spheres, solid colours
+    assert feat("the_next_week", 1) == F.SF_MOTION | F.SF_TEXTURES   # bouncing spheres on a checker ground
+    assert feat("the_next_week", 3) == F.SF_TEXTURES        # earth (image texture)
+    assert feat("the_next_week", 4) == F.SF_TEXTURES        # perlin
+    assert feat("the_next_week", 5) == F.SF_QUADS
+    assert feat("the_next_week", 7) == F.SF_QUADS           # cornell box
+    assert feat("the_next_week", 8) == F.SF_QUADS | F.SF_MEDIA   # cornell smoke
+    assert feat("the_next_week", 9) == F.SF_ALL             # final scene
+    assert feat("the_rest_of_your_life") == F.SF_QUADS      # cornell box + glass sphere
+
+
 def test_flattener_rejects_malformed_descriptions():
     b = R.DescBuilder()
     m = b.lambertian((0.5, 0.5, 0.5))

@@ -160,3 +160,30 @@ def test_teardown_in_either_order_is_safe():
     g2 = c2.scene(s.desc)
     g2.close()
     c2.close()
+
+
+@pytest.mark.parametrize("book,scene_no,feat", [
+    ("in_one_weekend", None, 0), ("the_next_week", 1, F.SF_MOTION | F.SF_TEXTURES), ("the_next_week", 4, F.SF_TEXTURES),
+    ("the_next_week", 5, F.SF_QUADS), ("the_next_week", 6, F.SF_QUADS | F.SF_TEXTURES),
+    ("the_next_week", 8, F.SF_QUADS | F.SF_MEDIA), ("the_next_week", 9, F.SF_ALL), ("the_rest_of_your_life", None, F.SF_QUADS)])
+def test_specialised_kernel_instance_equals_the_general_one(ctx, book, scene_no, feat, monkeypatch):
+    """A scene runs on the smallest render_kernel<INTEGRATOR, FEAT> covering it; RRT_KERNEL=full forces
+    the SF_ALL instance.  Same seed, same Philox keys: the two frames agree up to the compiler's
+    different FMA contraction in the two instances (a handful of paths that flip at a boundary)."""
+    s = R.BookScene(book, scene_no, overrides=dict(image_width=96, samples_per_pixel=64, max_depth=12))
+    gs = ctx.scene(s.desc)
+    a = ctx.render(gs, s.camera, s.integrator, seed=5).astype(np.float64)
+    assert ctx.stats()["kernel_features"] == feat
+    monkeypatch.setenv("RRT_KERNEL", "full")
+    full = R.Context(0)
+    monkeypatch.delenv("RRT_KERNEL")
+    gf = full.scene(s.desc)
+    b = full.render(gf, s.camera, s.integrator, seed=5).astype(np.float64)
+    assert full.stats()["kernel_features"] == F.SF_ALL
+    gf.close(); full.close(); gs.close()
+    assert np.array_equal(a[..., 3], b[..., 3])
+    ma, mb = a[..., :3].mean(axis=(0, 1)), b[..., :3].mean(axis=(0, 1))
+    assert np.all(np.abs(ma - mb) <= 2e-3 * np.maximum(mb, 1e-6)), (ma, mb)
+    lum_a, lum_b = a[..., :3].sum(axis=2), b[..., :3].sum(axis=2)
+    differs = np.abs(lum_a - lum_b) > 1e-3 * np.maximum(lum_b, 1e-3)
+    assert differs.mean() < 0.05, differs.mean()
