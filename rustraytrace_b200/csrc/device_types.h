@@ -65,7 +65,8 @@ enum SceneFeature {
   SF_QUADS = 2,     // quads in the BVH
   SF_MEDIA = 4,     // constant media
   SF_TEXTURES = 8,  // a material whose texture is not a solid colour (checker / image / noise)
-  SF_ALL = 15
+  SF_NOISE = 16,    // a Perlin noise texture: its turbulence loop alone costs 16 registers (80 instead of 64)
+  SF_ALL = 31
 };
 
 struct DevMaterial {  // 32 B

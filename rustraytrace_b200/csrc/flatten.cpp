@@ -637,6 +637,8 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
   for (const BakedPrim& p : P) if (p.kind != PRIM_SPHERE) out.features |= SF_QUADS;
   if (!out.media.empty()) out.features |= SF_MEDIA;
   for (const DevMaterial& m : out.materials) if (m.tex >= 0) out.features |= SF_TEXTURES;  // solid colours were folded into albedo
+  if (out.features & SF_TEXTURES)
+    for (const DevTexture& t : out.textures) if (t.kind == RRT_T_NOISE) out.features |= SF_NOISE;
   if (P.empty()) { out.root_ref = make_leaf_ref(0, 0, 0); return RRT_OK; }
   int ns = 0, nq = 0;
   for (const BakedPrim& p : P) (p.kind == PRIM_SPHERE ? ns : nq)++;

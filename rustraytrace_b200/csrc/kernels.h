@@ -25,10 +25,10 @@ struct ProbeArgs {
   double* t;
 };
 
-// Resident CTAs per SM each render kernel instance is compiled for (its register budget).  Without
-// textures and moving spheres the kernel fits 64 registers spill-free: 8 CTAs, 32 warps per SM.
-// Perlin/image/checker lookups and the time-dependent sphere centre push it to 80 registers
-// (6 CTAs); 72 registers spill there and measured within 1 % (profiles/README.md).
+// Resident CTAs per SM each render kernel instance is compiled for (its register budget).  Every
+// instance without Perlin noise fits 64 registers spill-free: 8 CTAs, 32 warps per SM.  The
+// turbulence loop (7 octaves of 8 gradient lookups) pushes an instance to 80 registers (6 CTAs);
+// 72 or 64 registers spill 100-170 bytes there and measured within 1 % (profiles/README.md).
 #ifndef RRT_MIN_BLOCKS_LEAN
 #define RRT_MIN_BLOCKS_LEAN 8
 #endif
@@ -36,7 +36,7 @@ struct ProbeArgs {
 #define RRT_MIN_BLOCKS 6
 #endif
 constexpr int render_min_blocks(int feat) {
-  return (feat & (SF_TEXTURES | SF_MOTION)) ? RRT_MIN_BLOCKS : RRT_MIN_BLOCKS_LEAN;
+  return (feat & SF_NOISE) ? RRT_MIN_BLOCKS : RRT_MIN_BLOCKS_LEAN;
 }
 
 // One compiled instance of render_kernel<INTEGRATOR, FEAT> (kernels_book{1,2,3}.cu).

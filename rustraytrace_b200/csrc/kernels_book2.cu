@@ -10,8 +10,10 @@ const RenderVariant* render_variants_book2(int* n) {
     {SF_TEXTURES, render_kernel<RRT_INT_BOOK2, SF_TEXTURES>},
     {SF_MOTION | SF_TEXTURES, render_kernel<RRT_INT_BOOK2, SF_MOTION | SF_TEXTURES>},
     {SF_QUADS, render_kernel<RRT_INT_BOOK2, SF_QUADS>},
-    {SF_QUADS | SF_TEXTURES, render_kernel<RRT_INT_BOOK2, SF_QUADS | SF_TEXTURES>},
     {SF_QUADS | SF_MEDIA, render_kernel<RRT_INT_BOOK2, SF_QUADS | SF_MEDIA>},
+    {SF_TEXTURES | SF_NOISE, render_kernel<RRT_INT_BOOK2, SF_TEXTURES | SF_NOISE>},
+    {SF_QUADS | SF_TEXTURES | SF_NOISE, render_kernel<RRT_INT_BOOK2, SF_QUADS | SF_TEXTURES | SF_NOISE>},
+    {SF_ALL & ~SF_NOISE, render_kernel<RRT_INT_BOOK2, SF_ALL & ~SF_NOISE>},
     {SF_ALL, render_kernel<RRT_INT_BOOK2, SF_ALL>},
   };
   *n = (int)(sizeof table / sizeof table[0]);

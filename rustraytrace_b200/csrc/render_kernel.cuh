@@ -162,7 +162,7 @@ __device__ __forceinline__ bool shade_step(const DevScene& S, const DevCamera& C
   if ((FEAT & SF_TEXTURES) && M.albedo.w != 0.0f && sf.is_sphere) sphere_uv(sf.n_obj, sf.u, sf.v);
   V3f att(M.albedo.x, M.albedo.y, M.albedo.z);
   const bool textured = M.kind == RRT_M_LAMBERTIAN || M.kind == RRT_M_ISOTROPIC || M.kind == RRT_M_DIFFUSE_LIGHT;
-  if ((FEAT & SF_TEXTURES) && textured && M.tex >= 0) att = texture_value(S, M.tex, sf.u, sf.v, sf.p);
+  if ((FEAT & SF_TEXTURES) && textured && M.tex >= 0) att = texture_value<FEAT>(S, M.tex, sf.u, sf.v, sf.p);
 
   V3f dir(0.0f, 0.0f, 0.0f);
   bool pdf_branch = false;

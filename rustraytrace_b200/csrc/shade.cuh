@@ -59,6 +59,7 @@ __device__ inline float perlin_turb(const DevPerlin* __restrict__ P, V3f p, int 
 }
 
 // ---- textures ---------------------------------------------------------------------------------
+template <int FEAT>
 __device__ inline V3f texture_value(const DevScene& S, int tex, float u, float v, V3f p) {
   for (int guard = 0; guard < 9; ++guard) {
     const DevTexture t = S.textures[tex];
@@ -82,6 +83,7 @@ __device__ inline V3f texture_value(const DevScene& S, int tex, float u, float v
       return V3f(s * px.x, s * px.y, s * px.z);
     }
     // NoiseTexture, texture.rs:121-126
+    if (!(FEAT & SF_NOISE)) return V3f(0.0f, 0.0f, 0.0f);  // unreachable: the flattener sets SF_NOISE for such scenes
     float turb = perlin_turb(S.perlins + t.a, p, 7);
     float c = 0.5f * (1.0f + sinf(t.v.w * p.z + 10.0f * turb));
     return V3f(c, c, c);

@@ -163,8 +163,8 @@ def test_teardown_in_either_order_is_safe():
 
 
 @pytest.mark.parametrize("book,scene_no,feat", [
-    ("in_one_weekend", None, 0), ("the_next_week", 1, F.SF_MOTION | F.SF_TEXTURES), ("the_next_week", 4, F.SF_TEXTURES),
-    ("the_next_week", 5, F.SF_QUADS), ("the_next_week", 6, F.SF_QUADS | F.SF_TEXTURES),
+    ("in_one_weekend", None, 0), ("the_next_week", 1, F.SF_MOTION | F.SF_TEXTURES), ("the_next_week", 3, F.SF_TEXTURES), ("the_next_week", 4, F.SF_TEXTURES | F.SF_NOISE),
+    ("the_next_week", 5, F.SF_QUADS), ("the_next_week", 6, F.SF_QUADS | F.SF_TEXTURES | F.SF_NOISE),
     ("the_next_week", 8, F.SF_QUADS | F.SF_MEDIA), ("the_next_week", 9, F.SF_ALL), ("the_rest_of_your_life", None, F.SF_QUADS)])
 def test_specialised_kernel_instance_equals_the_general_one(ctx, book, scene_no, feat, monkeypatch):
     """A scene runs on the smallest render_kernel<INTEGRATOR, FEAT> covering it; RRT_KERNEL=full forces
