@@ -6,7 +6,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 tag = sys.argv[1]
 d = json.load(open(os.path.join(ROOT, "profiles", f"configs_{tag}.json")))
-ref = {"C2": "643 (same scene, 128 spp)"}
+ref = {"C2": "652 (same scene, 128 spp)"}
 for k, v in d.items():
     mean = max(abs(x) for x in v["mean_rel_diff"]) * 100
     print(f"| {k} {v['workload']} | {v['paths']:.3g} | {v['cpu_oracle_mpaths_s']} ({v['cpu_threads']}) | {ref.get(k, '—')} | "
