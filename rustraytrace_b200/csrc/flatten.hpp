@@ -31,9 +31,12 @@ struct FlatScene {
 };
 
 // Returns RRT_OK or a negative rrt_status with `err` filled.
+#ifndef RRT_SINGLE_LEAF_MAX
+#define RRT_SINGLE_LEAF_MAX 16
+#endif
 // single_leaf_max: scenes with at most this many primitives become one root leaf (brute force).
 int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err,
-                  int single_leaf_max = 16, int max_leaf = 4);
+                  int single_leaf_max = RRT_SINGLE_LEAF_MAX, int max_leaf = 4);
 
 // Camera::initialize (camera.rs:108-154) -> device camera blocks.  Returns image height.
 int camera_initialize(const rrt_camera* cam, DevCamera& c32, DevCamera64& c64);
