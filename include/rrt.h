@@ -168,9 +168,9 @@ typedef struct rrt_stats {
   int32_t n_prims, n_bvh_nodes, n_media, n_lights;
   int32_t sm_count;
   int32_t kernel_features; /* feature set of the render-kernel instance the last call ran: bit 0 moving
-                            * spheres, 1 quads, 2 constant media, 3 non-solid textures, 4 Perlin noise
-                            * (31 = the general instance); a scene runs on the smallest instance covering it.
-                            * RRT_KERNEL=full in the environment at rrt_init forces 31 (debugging). */
+                            * spheres, 1 quads, 2 constant media, 3 non-solid textures, 4 Perlin noise,
+                            * 5 box leaves (63 = the general instance); a scene runs on the smallest instance covering it.
+                            * RRT_KERNEL=full in the environment at rrt_init forces 63 (debugging). */
 } rrt_stats;
 
 typedef struct rrt_ctx rrt_ctx;

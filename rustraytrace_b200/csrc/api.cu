@@ -164,6 +164,7 @@ int rrt_scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out) {
   int rc = RRT_OK;
   if ((rc = upload(sc, F.prims, &D.prims)) || (rc = upload(sc, F.prims64, &D.prims64)) ||
       (rc = upload(sc, F.nodes, &D.nodes)) || (rc = upload(sc, F.bprims, &D.bprims)) ||
+      (rc = upload(sc, F.boxes, &D.boxes)) ||
       (rc = upload(sc, F.materials, &D.materials)) || (rc = upload(sc, F.textures, &D.textures)) ||
       (rc = upload(sc, F.images, &D.images)) || (rc = upload(sc, F.texels, &texels)) ||
       (rc = upload(sc, F.perlins, &D.perlins)) || (rc = upload(sc, F.media, &D.media)) ||
@@ -468,6 +469,10 @@ extern "C" int rrt_flatten_check(const rrt_scene_desc* desc, int32_t* n_prims, i
   std::vector<int> node_seen(nn, 0);
   auto mark_leaf = [&](int ref) -> bool {
     int leaf = ~ref, first = leaf >> 8, ns = (leaf >> 4) & 15, nq = leaf & 15;
+    if ((leaf & 0xFF) == LEAF_BOX_MARK) {  // box leaf: six quads named by the box record
+      if (first < 0 || 2 * first + 1 >= (int)F.boxes.size()) return false;
+      first = as_int(F.boxes[2 * first].w); ns = 0; nq = 6;
+    }
     if (first < 0 || first + ns + nq > F.n_prims) return false;
     for (int k = first; k < first + ns + nq; ++k) seen[k]++;
     return true;

@@ -40,6 +40,11 @@ enum PrimFlags { PF_UV_ROTATED = 1 };
 // n0 = (c0.c.x, c1.c.x, c0.c.y, c1.c.y)   n1 = (c0.c.z, c1.c.z, c0.e.x, c1.e.x)
 // n2 = (c0.e.y, c1.e.y, c0.e.z, c1.e.z)   n3 = (ref0, ref1, 0, 0) as int bits
 // ref >= 0: inner node index.  ref < 0: leaf, ~ref = (first << 8) | (n_spheres << 4) | n_quads.
+// Box leaf: ~ref = (box << 8) | 0xFF.  The six quads of an axis-aligned box (quad.rs box_()) are one leaf;
+// boxes[2*box] = (lo.xyz, first as int bits), boxes[2*box+1] = (hi.xyz, 0); the quads sit at
+// first .. first+5 in face order -x, +x, -y, +y, -z, +z.  The f32 kernel slab-tests the box, runs the
+// real quad test on the entry face only, and falls back to all six whenever that is not conclusive.
+static const int LEAF_BOX_MARK = 0xFF;
 static const int LEAF_MAX_PER_KIND = 15;
 inline
 #if defined(__CUDACC__)
@@ -66,7 +71,8 @@ enum SceneFeature {
   SF_MEDIA = 4,     // constant media
   SF_TEXTURES = 8,  // a material whose texture is not a solid colour (checker / image / noise)
   SF_NOISE = 16,    // a Perlin noise texture: its turbulence loop alone costs 16 registers (80 instead of 64)
-  SF_ALL = 31
+  SF_BOXES = 32,    // box leaves: the six quads of an axis-aligned box_() behind one slab test
+  SF_ALL = 63
 };
 
 struct DevMaterial {  // 32 B
@@ -135,6 +141,7 @@ struct DevScene {
   const float4* prims;
   const float4* nodes;
   const float4* bprims;
+  const float4* boxes;   // two float4 per box leaf
   const double* prims64;
   const DevMaterial* materials;
   const DevTexture* textures;

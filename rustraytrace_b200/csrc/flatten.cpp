@@ -41,6 +41,13 @@ struct BakedPrim {
   D3 Q, u, v, n, w; double d = 0, area = 0;  // quad
   double uvcos = 1, uvsin = 0;
   double lo[3], hi[3];
+  int box = -1, face = -1;   // member of box group `box`, face slot 0..5 = -x,+x,-y,+y,-z,+z
+};
+
+// Six quads that are exactly the faces of one axis-aligned box (quad.rs box_() under translations only).
+struct BoxGroup {
+  int member[6];      // index into the world prim list, by face slot
+  double lo[3], hi[3];
 };
 
 void pad_axis(double& lo, double& hi) {  // Aabb::pad_to_minimums, aabb.rs:107-118
@@ -265,10 +272,59 @@ struct Walker {
   std::vector<BakedPrim> world;
   std::vector<BakedPrim> boundary;
   std::vector<BakedMedium> media;
+  std::vector<BoxGroup> boxes;   // groups found in `world`
   std::string err;
   int status = RRT_OK;
 
   bool fail(int st, const std::string& m) { if (status == RRT_OK) { status = st; err = m; } return false; }
+
+  // Are out[first..first+6) the six faces of one axis-aligned box?  Then they become one BVH leaf.
+  void find_box(std::vector<BakedPrim>& out, size_t first) {
+    BoxGroup g;
+    for (int a = 0; a < 3; ++a) { g.lo[a] = std::numeric_limits<double>::infinity(); g.hi[a] = -g.lo[a]; }
+    int axis_of[6];
+    double plane[6], rlo[6][3], rhi[6][3];
+    for (int k = 0; k < 6; ++k) {
+      const BakedPrim& p = out[first + k];
+      if (p.kind != PRIM_QUAD) return;
+      int ua = -1, va = -1;
+      for (int a = 0; a < 3; ++a) {
+        if (p.u[a] != 0.0) { if (ua >= 0) return; ua = a; }
+        if (p.v[a] != 0.0) { if (va >= 0) return; va = a; }
+      }
+      if (ua < 0 || va < 0 || ua == va) return;
+      axis_of[k] = 3 - ua - va;
+      plane[k] = p.Q[axis_of[k]];
+      D3 far = p.Q + p.u + p.v;
+      for (int a = 0; a < 3; ++a) {
+        rlo[k][a] = std::min(p.Q[a], far[a]); rhi[k][a] = std::max(p.Q[a], far[a]);
+        g.lo[a] = std::min(g.lo[a], rlo[k][a]); g.hi[a] = std::max(g.hi[a], rhi[k][a]);
+      }
+    }
+    for (int a = 0; a < 3; ++a) if (!(g.hi[a] > g.lo[a])) return;
+    for (int s = 0; s < 6; ++s) g.member[s] = -1;
+    for (int k = 0; k < 6; ++k) {
+      const int ax = axis_of[k];
+      const double ext = g.hi[ax] - g.lo[ax], tol = 1e-9 * std::max(1.0, std::fabs(g.hi[ax]) + std::fabs(g.lo[ax]));
+      int side;
+      if (std::fabs(plane[k] - g.lo[ax]) <= tol) side = 0;
+      else if (std::fabs(plane[k] - g.hi[ax]) <= tol) side = 1;
+      else return;
+      (void)ext;
+      for (int a = 0; a < 3; ++a) {   // the face must span the whole box in its own two axes
+        if (a == ax) continue;
+        const double t2 = 1e-9 * std::max(1.0, std::fabs(g.hi[a]) + std::fabs(g.lo[a]));
+        if (std::fabs(rlo[k][a] - g.lo[a]) > t2 || std::fabs(rhi[k][a] - g.hi[a]) > t2) return;
+      }
+      if (g.member[2 * ax + side] >= 0) return;
+      g.member[2 * ax + side] = (int)(first + k);
+    }
+    for (int s = 0; s < 6; ++s) {
+      out[g.member[s]].box = (int)boxes.size();
+      out[g.member[s]].face = s;
+    }
+    boxes.push_back(g);
+  }
 
   bool walk(int idx, const Xform& X, std::vector<BakedPrim>& out, int depth, bool in_boundary) {
     if (idx < 0 || idx >= d->n_hittables) return fail(RRT_ERR_INVALID, "hittable index out of range");
@@ -298,8 +354,10 @@ struct Walker {
           ref.build(kids, 0, kids.size(), ordered);
           kids.swap(ordered);
         }
+        const size_t before = out.size();
         for (int k : kids)
           if (!walk(k, X, out, depth + 1, in_boundary)) return false;
+        if (!in_boundary && kids.size() == 6 && out.size() == before + 6) find_box(out, before);
         return true;
       }
       case RRT_H_TRANSLATE: {  // hittable.rs:86-93: p_parent = p_child + offset
@@ -336,6 +394,8 @@ struct Walker {
 // ------------------------------------------------------------------------------------------------
 // BVH: binary, full-sweep SAH over the three axes (host, once per scene).  Not the reference's
 // 12-bucket builder (bvh.rs:34-156) — the closest hit does not depend on the tree.
+enum { ITEM_BOX = 2 };  // build item standing for a BoxGroup (BakedPrim::kind beyond PRIM_SPHERE / PRIM_QUAD)
+
 struct BNode {
   double lo[3], hi[3];
   int left = -1, right = -1;   // children (BNode indices) or -1
@@ -366,7 +426,10 @@ struct Builder {
   }
   bool leaf_ok(int first, int count) const {
     int ns = 0, nq = 0;
-    for (int i = first; i < first + count; ++i) (P[order[i]].kind == PRIM_SPHERE ? ns : nq)++;
+    for (int i = first; i < first + count; ++i) {
+      if (P[order[i]].kind == ITEM_BOX && count > 1) return false;  // a box group is a leaf of its own
+      (P[order[i]].kind == PRIM_SPHERE ? ns : nq)++;
+    }
     return ns <= LEAF_MAX_PER_KIND && nq <= LEAF_MAX_PER_KIND;
   }
   int build(int first, int count, int depth) {
@@ -375,7 +438,7 @@ struct Builder {
     nodes.push_back(BNode());
     bounds(first, count, nodes[me].lo, nodes[me].hi);
     nodes[me].first = first; nodes[me].count = count;
-    if (count <= 1 || (count <= max_leaf && depth >= 40)) return me;
+    if (count <= 1 || (count <= max_leaf && depth >= 40 && leaf_ok(first, count))) return me;
     double parent_area = area(nodes[me].lo, nodes[me].hi);
     double best_cost = std::numeric_limits<double>::infinity();
     int best_axis = -1, best_split = -1;
@@ -643,14 +706,31 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
   int ns = 0, nq = 0;
   for (const BakedPrim& p : P) (p.kind == PRIM_SPHERE ? ns : nq)++;
   bool single = (int)P.size() <= single_leaf_max && ns <= LEAF_MAX_PER_KIND && nq <= LEAF_MAX_PER_KIND;
-  Builder B(P, single ? (int)P.size() : max_leaf);
+  // build items: every primitive, except that the six quads of a box group are one item
+  const bool use_boxes = !single && !w.boxes.empty() && !std::getenv("RRT_NO_BOX_LEAVES");
+  std::vector<BakedPrim> items;
+  std::vector<int> item_src;   // index into P, or -1 - box group index
+  for (size_t i = 0; i < P.size(); ++i)
+    if (!use_boxes || P[i].box < 0) { items.push_back(P[i]); item_src.push_back((int)i); }
+  if (use_boxes) {
+    out.features |= SF_BOXES;
+    for (size_t g = 0; g < w.boxes.size(); ++g) {
+      BakedPrim it;
+      it.kind = ITEM_BOX; it.box = (int)g;
+      for (int a = 0; a < 3; ++a) { it.lo[a] = w.boxes[g].lo[a]; it.hi[a] = w.boxes[g].hi[a]; }
+      for (int s = 0; s < 6; ++s)   // the faces' own (padded) bounds, as the reference's list box has them
+        for (int a = 0; a < 3; ++a) { it.lo[a] = std::min(it.lo[a], P[w.boxes[g].member[s]].lo[a]); it.hi[a] = std::max(it.hi[a], P[w.boxes[g].member[s]].hi[a]); }
+      items.push_back(it); item_src.push_back(-1 - (int)g);
+    }
+  }
+  Builder B(items, single ? (int)items.size() : max_leaf);
   int root = 0;
   if (single) {
     B.nodes.push_back(BNode());
-    B.bounds(0, (int)P.size(), B.nodes[0].lo, B.nodes[0].hi);
-    B.nodes[0].first = 0; B.nodes[0].count = (int)P.size();
+    B.bounds(0, (int)items.size(), B.nodes[0].lo, B.nodes[0].hi);
+    B.nodes[0].first = 0; B.nodes[0].count = (int)items.size();
   } else {
-    root = B.build(0, (int)P.size(), 0);
+    root = B.build(0, (int)items.size(), 0);
   }
   out.bvh_depth = B.max_depth_seen;
   // leaf -> contiguous prim run (spheres first, then quads); prims emitted in `order` sequence
@@ -665,10 +745,23 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
     std::sort(leaves.begin(), leaves.end(), [&](int a, int b) { return B.nodes[a].first < B.nodes[b].first; });
     for (int li : leaves) {
       const BNode& n = B.nodes[li];
+      if (n.count == 1 && items[B.order[n.first]].kind == ITEM_BOX) {  // box leaf: six quads in face order + a box record
+        const BoxGroup& g = w.boxes[items[B.order[n.first]].box];
+        float lo[3], hi[3], fc[3], fh[3];
+        box32(items[B.order[n.first]].lo, items[B.order[n.first]].hi, fc, fh);   // padded, rounded outward
+        for (int a = 0; a < 3; ++a) { lo[a] = fc[a] - fh[a]; hi[a] = fc[a] + fh[a]; }
+        float4 b0 = f4(lo[0], lo[1], lo[2], 0), b1 = f4(hi[0], hi[1], hi[2], 0);
+        std::memcpy(&b0.w, &emitted, 4);
+        leaf_ref[li] = ~(((int)(out.boxes.size() / 2) << 8) | LEAF_BOX_MARK);
+        out.boxes.push_back(b0); out.boxes.push_back(b1);
+        for (int s = 0; s < 6; ++s) { emit_prim32(P[g.member[s]], out.prims); emit_prim64(P[g.member[s]], out.prims64); }
+        emitted += 6;
+        continue;
+      }
       int s = 0, q = 0;
       for (int pass = 0; pass < 2; ++pass)
         for (int k = n.first; k < n.first + n.count; ++k) {
-          const BakedPrim& p = P[B.order[k]];
+          const BakedPrim& p = items[B.order[k]];
           if (p.kind == pass) { emit_prim32(p, out.prims); emit_prim64(p, out.prims64); (pass == 0 ? s : q)++; }
         }
       leaf_ref[li] = make_leaf_ref(emitted, s, q);

@@ -14,6 +14,7 @@ namespace rrt {
 struct FlatScene {
   std::vector<float4> prims;      // 4 per prim
   std::vector<double> prims64;    // 16 per prim
+  std::vector<float4> boxes;     // box leaves, two float4 each (device_types.h)
   std::vector<float4> nodes;      // 4 per inner node
   std::vector<float4> bprims;     // 4 per medium-boundary prim
   std::vector<DevMaterial> materials;

@@ -106,10 +106,49 @@ __device__ inline void quad_hit32(const float4* __restrict__ prims, int i, const
   h.prim = i | PRIM_QUAD_BIT;
 }
 
+__device__ inline float safe_rcp(float d) {
+  // a zero direction component would turn the slab products into NaN (0 * inf); aabb.rs:58 has
+  // the same hazard in f64 but never meets an exact zero.  Clamp instead.
+  float ad = fabsf(d);
+  return 1.0f / (ad > 1e-30f ? d : copysignf(1e-30f, d));
+}
+
+// Box leaf (device_types.h): the six quads of an axis-aligned box behind one slab test.  The slab
+// only culls and names the entry face; the hit itself is always quad_hit32's, so t, the interior
+// test and the tie rules are those of the six-quad list the reference holds (quad.rs box_()).
+// Whenever the entry face does not settle it (origin inside, grazing an edge) all six are tested.
+__device__ inline void box_leaf_hit32(const float4* __restrict__ prims, const float4* __restrict__ boxes, int box,
+                                      const Ray32& r, V3f id, float tmin, int skip, Hit32& h) {
+  const float4 b0 = ldg4(boxes + 2 * box), b1 = ldg4(boxes + 2 * box + 1);
+  const int first = __float_as_int(b0.w);
+  const unsigned from = (unsigned)(skip - first);
+  if (from < 6u) {  // the ray starts on one of this box's faces
+    const float dk = (from >> 1) == 0 ? r.d.x : ((from >> 1) == 1 ? r.d.y : r.d.z);
+    if ((from & 1u) ? dk > 0.0f : dk < 0.0f) return;  // leaving outward: a convex box is not met again
+  } else {
+    const float x0 = (b0.x - r.o.x) * id.x, x1 = (b1.x - r.o.x) * id.x;
+    const float y0 = (b0.y - r.o.y) * id.y, y1 = (b1.y - r.o.y) * id.y;
+    const float z0 = (b0.z - r.o.z) * id.z, z1 = (b1.z - r.o.z) * id.z;
+    const float nx = fminf(x0, x1), ny = fminf(y0, y1), nz = fminf(z0, z1);
+    const float near = fmaxf(fmaxf(nx, ny), nz);
+    const float far = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
+    if (!(near <= far * 1.0000004f) || far < tmin || near > h.t * 1.0000004f) return;  // the box record is padded
+    if (near >= tmin) {  // origin outside: the closest face is the one the ray enters through
+      const int axis = near == nx ? 0 : (near == ny ? 1 : 2);
+      const float da = axis == 0 ? r.d.x : (axis == 1 ? r.d.y : r.d.z);
+      const int face = first + 2 * axis + (da > 0.0f ? 0 : 1);
+      quad_hit32(prims, face, r, tmin, skip, h);
+      if (h.prim == (face | PRIM_QUAD_BIT)) return;
+    }
+  }
+  for (int f = 0; f < 6; ++f) quad_hit32(prims, first + f, r, tmin, skip, h);
+}
+
 // One leaf: a contiguous run, spheres first.  ~ref = (first << 8) | (nsph << 4) | nquad.
 template <int FEAT>
-__device__ inline void leaf_hit32(const float4* __restrict__ prims, int leaf, const Ray32& r, float a,
-                                  float inv_a, float tmin, int skip, bool motion, Hit32& h) {
+__device__ inline void leaf_hit32(const float4* __restrict__ prims, const float4* __restrict__ boxes, int leaf,
+                                  const Ray32& r, V3f id, float a, float inv_a, float tmin, int skip, bool motion, Hit32& h) {
+  if ((FEAT & SF_BOXES) && (leaf & 0xFF) == LEAF_BOX_MARK) { box_leaf_hit32(prims, boxes, leaf >> 8, r, id, tmin, skip, h); return; }
   int first = leaf >> 8, ns = (leaf >> 4) & 15, nq = leaf & 15;
   for (int k = 0; k < ns; ++k) sphere_hit32(prims, first + k, r, a, inv_a, tmin, skip, motion, h);
   first += ns;
@@ -117,12 +156,6 @@ __device__ inline void leaf_hit32(const float4* __restrict__ prims, int leaf, co
     for (int k = 0; k < nq; ++k) quad_hit32(prims, first + k, r, tmin, skip, h);
 }
 
-__device__ inline float safe_rcp(float d) {
-  // a zero direction component would turn the slab products into NaN (0 * inf); aabb.rs:58 has
-  // the same hazard in f64 but never meets an exact zero.  Clamp instead.
-  float ad = fabsf(d);
-  return 1.0f / (ad > 1e-30f ? d : copysignf(1e-30f, d));
-}
 
 // Packed FP32 FMA (Blackwell fma.rn.f32x2 -> SASS FFMA2): both halves of a 64-bit register pair in
 // one issue slot; ptxas folds negation, |x| and a scalar broadcast into the operand modifiers.
@@ -170,7 +203,7 @@ __device__ inline void world_hit32(const DevScene& S, const Ray32& r, float tmin
   const bool motion = (FEAT & SF_MOTION) && S.has_motion != 0;
   int cur = S.root_ref;
   if (cur < 0) {  // the whole scene is one leaf: brute force, uniform control flow
-    leaf_hit32<FEAT>(S.prims, ~cur, r, a, inv_a, tmin, skip, motion, h);
+    leaf_hit32<FEAT>(S.prims, S.boxes, ~cur, r, V3f(0.0f, 0.0f, 0.0f), a, inv_a, tmin, skip, motion, h);  // a root leaf is never a box leaf
     return;
   }
   const float idx = safe_rcp(r.d.x), idy = safe_rcp(r.d.y), idz = safe_rcp(r.d.z);
@@ -211,7 +244,7 @@ __device__ inline void world_hit32(const DevScene& S, const Ray32& r, float tmin
     }
     if (done) break;
     if (cur < 0) {
-      leaf_hit32<FEAT>(S.prims, ~cur, r, a, inv_a, tmin, skip, motion, h);
+      leaf_hit32<FEAT>(S.prims, S.boxes, ~cur, r, V3f(idx, idy, idz), a, inv_a, tmin, skip, motion, h);
       if (sp == 0) break;
       cur = stack[--sp];
     }
@@ -310,6 +343,11 @@ __device__ inline void quad_hit64(const double* __restrict__ q, int i, V3d o, V3
 }
 
 __device__ inline void leaf_hit64(const DevScene& S, int leaf, V3d o, V3d d, double tmin, Hit64& h) {
+  if ((leaf & 0xFF) == LEAF_BOX_MARK) {  // box leaf: the probe tests the six quads, no shortcut
+    int first = __float_as_int(ldg4(S.boxes + 2 * (leaf >> 8)).w);
+    for (int k = 0; k < 6; ++k) quad_hit64(S.prims64, first + k, o, d, tmin, S.prims, h);
+    return;
+  }
   int first = leaf >> 8, ns = (leaf >> 4) & 15, nq = leaf & 15;
   for (int k = 0; k < ns; ++k) sphere_hit64(S.prims64, first + k, o, d, tmin, S.prims, h);
   first += ns;

@@ -101,6 +101,24 @@ def test_scene_feature_bits_select_the_kernel_instance():
     assert feat("the_rest_of_your_life") == F.SF_QUADS      # cornell box + glass sphere
 
 
+def test_axis_aligned_boxes_become_box_leaves(monkeypatch):
+    """The 400 ground boxes of the book-2 final scene (quad.rs box_(), 6 quads each) are one BVH leaf
+    each; the rotated boxes of the Cornell scenes are not axis-aligned and stay plain quads."""
+    s = R.BookScene("the_next_week", 9, overrides=dict(image_width=64))
+    with_boxes = R.flatten_check(s.desc)
+    assert R.scene_features(s.desc) & F.SF_BOXES
+    monkeypatch.setenv("RRT_NO_BOX_LEAVES", "1")
+    without = R.flatten_check(s.desc)
+    assert not (R.scene_features(s.desc) & F.SF_BOXES)
+    monkeypatch.delenv("RRT_NO_BOX_LEAVES")
+    assert with_boxes["n_prims"] == without["n_prims"] == 3407
+    # 400 boxes: 2400 single-quad leaves and their 2000 inner nodes collapse into 400 leaves
+    assert without["n_nodes"] - with_boxes["n_nodes"] >= 1700
+    for no in (7, 8):
+        c = R.BookScene("the_next_week", no, overrides=dict(image_width=64))
+        assert not (R.scene_features(c.desc) & F.SF_BOXES)
+
+
 def test_flattener_rejects_malformed_descriptions():
     b = R.DescBuilder()
     m = b.lambertian((0.5, 0.5, 0.5))
