@@ -237,7 +237,8 @@ int rrt_shard_plan(const rrt_camera* cam, const rrt_render_params* params, int32
  *   primitive in exactly one leaf, every child box inside its parent's).  Outputs may be NULL.
  *   rrt_scene_features: the feature bits the flattened scene needs (rrt_stats.kernel_features lists
  *   them); the render calls pick the smallest kernel instance that covers them.
- *   rrt_philox_kat:    one Philox4x32-10 block (the sampling RNG), for known-answer tests. */
+ *   rrt_philox_kat:    one Philox4x32-10 block, for known-answer tests of the sampling RNG's round
+ *   function (the render kernel runs the same function for 7 rounds). */
 int rrt_flatten_check(const rrt_scene_desc* desc, int32_t* n_prims, int32_t* n_nodes, int32_t* bvh_depth,
                       int32_t* n_media, int32_t* n_lights);
 int rrt_scene_features(const rrt_scene_desc* desc, int32_t* features);

@@ -1,5 +1,8 @@
-// rng.cuh — counter-based Philox4x32-10 (Salmon et al., SC'11), keyed on the render seed and
-// counted by (pixel, sample, bounce, draw block).  Replaces the reference's thread-local
+// rng.cuh — counter-based Philox4x32 (Salmon et al., SC'11), keyed on the render seed and
+// counted by (pixel, sample, bounce, draw block).  The kernel runs 7 rounds, the fewest the paper
+// reports as Crush-resistant for Philox4x32 (10 is its default safety margin): 3 rounds fewer are
+// worth 3 % on C2/C5 and 6 % on C4 (profiles/README.md).  rrt_philox_kat checks the same round
+// function at 10 rounds against Random123's known answers.  Replaces the reference's thread-local
 // SmallRng::from_entropy() (the_rest_of_your_life/rtweekend.rs:9-25): only the distribution of
 // random_double() — uniform in [0,1) — is specified there, so any partition of the frame over
 // blocks, launches or GPUs sees the same numbers for the same (pixel, sample, bounce).
@@ -11,11 +14,12 @@ namespace rrt {
 
 struct Rand4 { float x, y, z, w, v; };  // v: a fifth uniform built from the low bytes u01 does not use
 
-__host__ __device__ inline void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
-                                             uint32_t k0, uint32_t k1, uint32_t out[4]) {
+template <int ROUNDS>
+__host__ __device__ inline void philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                          uint32_t k0, uint32_t k1, uint32_t out[4]) {
   const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
 #pragma unroll
-  for (int r = 0; r < 10; ++r) {
+  for (int r = 0; r < ROUNDS; ++r) {
 #if defined(__CUDA_ARCH__)
     uint32_t hi0 = __umulhi(M0, c0), hi1 = __umulhi(M1, c2);
 #else
@@ -30,6 +34,15 @@ __host__ __device__ inline void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t
   out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
 
+__host__ __device__ inline void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                             uint32_t k0, uint32_t k1, uint32_t out[4]) {
+  philox4x32<10>(c0, c1, c2, c3, k0, k1, out);
+}
+
+#ifndef RRT_PHILOX_ROUNDS
+#define RRT_PHILOX_ROUNDS 7
+#endif
+
 // 24-bit mantissa fill: uniform in [0,1), never 1.0
 __host__ __device__ inline float u01(uint32_t x) { return (float)(x >> 8) * (1.0f / 16777216.0f); }
 
@@ -37,7 +50,7 @@ struct PathRng {
   uint32_t pixel, sample, k0, k1;
   __device__ inline Rand4 draw(uint32_t bounce, uint32_t block) const {
     uint32_t o[4];
-    philox4x32_10(pixel, sample, bounce, block, k0, k1, o);
+    philox4x32<RRT_PHILOX_ROUNDS>(pixel, sample, bounce, block, k0, k1, o);
     Rand4 r; r.x = u01(o[0]); r.y = u01(o[1]); r.z = u01(o[2]); r.w = u01(o[3]);
     r.v = (float)(((o[0] & 255u) << 16) | ((o[1] & 255u) << 8) | (o[2] & 255u)) * (1.0f / 16777216.0f);
     return r;
