@@ -114,8 +114,11 @@ __device__ __forceinline__ bool shade_step(const DevScene& S, const DevCamera& C
   int medium = -1;
   if ((FEAT & SF_MEDIA) && S.n_media > 0) {  // ConstantMedium::hit, constant_medium.rs:39-79
     const float a = dot(ray.d, ray.d), inv_a = 1.0f / a;
+    // free-flight draws: medium 0 takes ra.v, medium 1 takes ra.w where the bounce does not use it (books
+    // 1-2: direction from ra.x, ra.y, roulette ra.z), so two media cost no second Philox block
+    const int first_rb = INTEGRATOR == RRT_INT_BOOK3 ? 1 : 2;
     Rand4 rb;
-    if (S.n_media > 1) rb = rng.draw((uint32_t)bounce, 1);
+    if (S.n_media > first_rb) rb = rng.draw((uint32_t)bounce, 1);
     for (int m = 0; m < S.n_media; ++m) {
       const DevMedium M = S.media[m];
       float t1, t2;
@@ -125,7 +128,8 @@ __device__ __forceinline__ bool shade_step(const DevScene& S, const DevCamera& C
       if (t2 > h.t) t2 = h.t;
       if (t1 >= t2) continue;
       if (t1 < 0.0f) t1 = 0.0f;
-      float xi = m == 0 ? ra.v : (m == 1 ? rb.x : (m == 2 ? rb.y : (m == 3 ? rb.z : rb.w)));
+      const int k = m - first_rb;  // index into the second block
+      float xi = m == 0 ? ra.v : (k < 0 ? ra.w : (k == 0 ? rb.x : (k == 1 ? rb.y : (k == 2 ? rb.z : rb.w))));
       float len = sqrtf(a);
       float inside = (t2 - t1) * len;
       float hit_distance = M.neg_inv_density * __logf(xi);
