@@ -40,6 +40,7 @@ struct rrt_ctx {
   float* accum = nullptr;  // grow-only frame buffer for the host-output entry points
   size_t accum_floats = 0;
   rrt_stats stats;
+  bool no_steal = false;              // RRT_NO_STEAL=1: lanes never take over neighbours' samples (debugging / A-B)
   bool force_full_kernel = false;     // RRT_KERNEL=full: always run the SF_ALL render kernel instance (include/rrt.h)
   std::vector<rrt_scene*> scenes;  // live scenes of this context (released by rrt_shutdown if the caller did not)
 };
@@ -96,6 +97,7 @@ int rrt_init(int device, rrt_ctx** out) {
   c->sm_count = prop.multiProcessorCount;
   const char* kv = std::getenv("RRT_KERNEL");
   c->force_full_kernel = kv && std::strcmp(kv, "full") == 0;
+  c->no_steal = std::getenv("RRT_NO_STEAL") != nullptr;
   CK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking), "cudaStreamCreate");
   c->stream = c->own_stream;
   for (auto& ev : c->ev) CK(cudaEventCreate(&ev), "cudaEventCreate");
@@ -263,17 +265,24 @@ int rrt_render_device(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, co
   const int n_samples = W.s_end - W.s_begin;
 
   const RenderVariant* variant = select_render_variant(p->integrator, sc->dev.features, c->force_full_kernel);
-  int bps = render_blocks_per_sm(variant);
+  // Sample stealing (render_kernel.cuh) pays wherever path cost varies inside a warp (C1 +20 %, C2/C3a
+  // +3.5 %, C5 +1-6 %).  Not for one- and two-primitive scenes (near-constant path cost; the shared
+  // counters cost 9 % on C3b) nor for the Perlin instances, which sit at their register limit (C4 -4 %).
+  const bool steal = sc->n_prims > 2 && !(variant->features & SF_NOISE) && !c->no_steal;
+  int bps = render_blocks_per_sm(variant, steal);
   if (bps < 1) return fail(RRT_ERR_CUDA, "kernel launch failed: render kernel does not fit on an SM");
   const int grid = c->sm_count * bps;
   const long long resident_warps = (long long)grid * (RRT_BLOCK / 32);
   long long chunks = 1;
   if (W.n_tiles > 0 && n_samples > 0) {
-    long long want = (48 * resident_warps + W.n_tiles - 1) / W.n_tiles;
-    long long cap = std::max(1, n_samples / 16);
+    // work items per resident warp / fewest samples per lane and item (measured: profiles/README.md):
+    // with stealing a short item has no intra-warp tail, so items can be smaller
+    long long want = ((steal ? 96 : 48) * resident_warps + W.n_tiles - 1) / W.n_tiles;
+    long long cap = std::max(1, n_samples / (steal ? 8 : 16));
     chunks = std::max(1LL, std::min(want, cap));
   }
   W.chunks = (int)chunks;
+  W.steal = steal ? 1 : 0;
   W.atomic_accum = chunks > 1 ? 1 : 0;
   A.accum = reinterpret_cast<float4*>(accum_dev);
   A.counter = c->counter;
@@ -285,7 +294,7 @@ int rrt_render_device(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, co
   int launches = 0;
   CK(cudaEventRecord(c->ev[1], c->stream), "cudaEventRecord");
   if (W.n_tiles > 0 && n_samples > 0) {
-    CK(launch_render(variant, A, grid, c->stream), "kernel launch failed");
+    CK(launch_render(variant, steal, A, grid, c->stream), "kernel launch failed");
     launches = 1;
   }
   CK(cudaEventRecord(c->ev[2], c->stream), "cudaEventRecord");

@@ -65,14 +65,14 @@ const RenderVariant* select_render_variant(int integrator, int features, bool fo
   return &t[n - 1];  // SF_ALL is the last entry of every table
 }
 
-cudaError_t launch_render(const RenderVariant* v, const RenderArgs& A, int grid, cudaStream_t st) {
+cudaError_t launch_render(const RenderVariant* v, bool steal, const RenderArgs& A, int grid, cudaStream_t st) {
   void* args[] = {const_cast<RenderArgs*>(&A)};
-  return cudaLaunchKernel(reinterpret_cast<const void*>(v->kernel), dim3(grid), dim3(RRT_BLOCK), args, 0, st);
+  return cudaLaunchKernel(reinterpret_cast<const void*>(steal ? v->kernel : v->kernel_own), dim3(grid), dim3(RRT_BLOCK), args, 0, st);
 }
 
-int render_blocks_per_sm(const RenderVariant* v) {
+int render_blocks_per_sm(const RenderVariant* v, bool steal) {
   int n = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, reinterpret_cast<const void*>(v->kernel), RRT_BLOCK, 0) != cudaSuccess) {
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, reinterpret_cast<const void*>(steal ? v->kernel : v->kernel_own), RRT_BLOCK, 0) != cudaSuccess) {
     cudaGetLastError();
     return 0;
   }

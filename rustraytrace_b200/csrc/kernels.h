@@ -42,7 +42,8 @@ constexpr int render_min_blocks(int feat) {
 // One compiled instance of render_kernel<INTEGRATOR, FEAT> (kernels_book{1,2,3}.cu).
 struct RenderVariant {
   int features;                 // SceneFeature bits the instance supports
-  void (*kernel)(RenderArgs);   // __global__ entry
+  void (*kernel)(RenderArgs);      // __global__ entry, lanes take over neighbours' samples (STEAL)
+  void (*kernel_own)(RenderArgs);  // every lane keeps to its own pixel
 };
 const RenderVariant* render_variants_book1(int* n);
 const RenderVariant* render_variants_book2(int* n);
@@ -50,8 +51,8 @@ const RenderVariant* render_variants_book3(int* n);
 
 // Smallest instance of the integrator covering `features` (force_full: the SF_ALL instance).
 const RenderVariant* select_render_variant(int integrator, int features, bool force_full);
-cudaError_t launch_render(const RenderVariant* v, const RenderArgs& A, int grid, cudaStream_t st);
-int render_blocks_per_sm(const RenderVariant* v);
+cudaError_t launch_render(const RenderVariant* v, bool steal, const RenderArgs& A, int grid, cudaStream_t st);
+int render_blocks_per_sm(const RenderVariant* v, bool steal);
 cudaError_t launch_probe(const ProbeArgs& A, int precision, cudaStream_t st);
 cudaError_t launch_probe64(const ProbeArgs& A, cudaStream_t st);  // probe64.cu (-fmad=false)
 cudaError_t launch_resolve(const float* accum, int n, int spp, unsigned char* rgb, cudaStream_t st);

@@ -6,8 +6,8 @@ namespace rrt {
 
 const RenderVariant* render_variants_book1(int* n) {
   static const RenderVariant table[] = {
-    {0, render_kernel<RRT_INT_BOOK1, 0>},
-    {SF_ALL, render_kernel<RRT_INT_BOOK1, SF_ALL>},
+    {0, render_kernel<RRT_INT_BOOK1, 0, true>, render_kernel<RRT_INT_BOOK1, 0, false>},
+    {SF_ALL, render_kernel<RRT_INT_BOOK1, SF_ALL, true>, render_kernel<RRT_INT_BOOK1, SF_ALL, false>},
   };
   *n = (int)(sizeof table / sizeof table[0]);
   return table;

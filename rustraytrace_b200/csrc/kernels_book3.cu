@@ -6,9 +6,9 @@ namespace rrt {
 
 const RenderVariant* render_variants_book3(int* n) {
   static const RenderVariant table[] = {
-    {SF_QUADS, render_kernel<RRT_INT_BOOK3, SF_QUADS>},
-    {SF_QUADS | SF_MEDIA, render_kernel<RRT_INT_BOOK3, SF_QUADS | SF_MEDIA>},
-    {SF_ALL, render_kernel<RRT_INT_BOOK3, SF_ALL>},
+    {SF_QUADS, render_kernel<RRT_INT_BOOK3, SF_QUADS, true>, render_kernel<RRT_INT_BOOK3, SF_QUADS, false>},
+    {SF_QUADS | SF_MEDIA, render_kernel<RRT_INT_BOOK3, SF_QUADS | SF_MEDIA, true>, render_kernel<RRT_INT_BOOK3, SF_QUADS | SF_MEDIA, false>},
+    {SF_ALL, render_kernel<RRT_INT_BOOK3, SF_ALL, true>, render_kernel<RRT_INT_BOOK3, SF_ALL, false>},
   };
   *n = (int)(sizeof table / sizeof table[0]);
   return table;

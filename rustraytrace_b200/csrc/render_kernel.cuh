@@ -251,7 +251,7 @@ __device__ __forceinline__ bool shade_step(const DevScene& S, const DevCamera& C
 }
 
 // ---- the megakernel ---------------------------------------------------------------------------------
-template <int INTEGRATOR, int FEAT>
+template <int INTEGRATOR, int FEAT, bool STEAL>
 __global__ void __launch_bounds__(RRT_BLOCK, render_min_blocks(FEAT))
 render_kernel(const __grid_constant__ RenderArgs A) {
   const DevScene& S = A.S;
@@ -281,6 +281,21 @@ render_kernel(const __grid_constant__ RenderArgs A) {
     rng.k0 = W.seed_lo; rng.k1 = W.seed_hi;
 
     V3f sum(0.0f, 0.0f, 0.0f);
+    // Sample stealing inside the warp: a lane that has traced all samples of its own pixel goes on
+    // with a neighbour's (shared-memory sample counters, one per pixel of the tile; foreign radiance
+    // goes through shared-memory adds), so the warp stays full until the whole tile's samples are
+    // handed out instead of waiting for its slowest pixel.  Every (pixel, sample) is still traced
+    // exactly once with its own Philox key.
+    __shared__ int sh_next[RRT_BLOCK];
+    __shared__ float sh_sum[3][RRT_BLOCK];
+    const int wbase = threadIdx.x & ~31;
+    if (STEAL) {
+      __syncwarp();
+      sh_next[threadIdx.x] = valid ? s0 : s1;
+      sh_sum[0][threadIdx.x] = 0.0f; sh_sum[1][threadIdx.x] = 0.0f; sh_sum[2][threadIdx.x] = 0.0f;
+      __syncwarp();
+    }
+    int tgt = lane;
     int s = s0;
     bool alive = false;
     Path P;
@@ -289,21 +304,41 @@ render_kernel(const __grid_constant__ RenderArgs A) {
     P.bounce = 0; P.skip = -1;
 
     for (;;) {
-      if (!alive) {  // this lane's path ended: start the next sample of its pixel
-        if (!valid || s >= s1) break;
-        generate_ray<INTEGRATOR, FEAT>(S, C, rng, px, py, s, P);
-        ++s;
+      if (!alive) {  // next sample of this lane's pixel, or of a neighbour's once its own are done
+        int s_new = s1;
+        if (STEAL) {
+          int tries = 0;
+          for (; tries < 32; ++tries) {
+            s_new = atomicAdd(&sh_next[wbase + tgt], 1);
+            if (s_new < s1) break;
+            tgt = (tgt + 1) & 31;
+          }
+          if (tries == 32) break;
+        } else {
+          if (!valid || s >= s1) break;
+          s_new = s++;
+        }
+        const int tx = px0 + (tgt & 7), ty = py0 + (tgt >> 3);
+        rng.pixel = (uint32_t)(ty * W.width + tx);
+        generate_ray<INTEGRATOR, FEAT>(S, C, rng, tx, ty, s_new, P);
         alive = true;
       }
       Hit32 h;
       h.t = CUDART_INF_F; h.prim = -1;
       world_hit32<FEAT>(S, P.ray, 0.001f, P.skip, h);  // world.hit(r, Interval::new(0.001, INFINITY)), camera.rs:189
       if (!shade_step<INTEGRATOR, FEAT>(S, C, rng, W.max_depth, h, P)) {
-        if (finite3(P.L)) sum = sum + P.L;  // a non-finite sample contributes nothing (color.rs:19-27)
+        if (finite3(P.L)) {  // a non-finite sample contributes nothing (color.rs:19-27)
+          if (!STEAL || tgt == lane) sum = sum + P.L;
+          else { atomicAdd(&sh_sum[0][wbase + tgt], P.L.x); atomicAdd(&sh_sum[1][wbase + tgt], P.L.y); atomicAdd(&sh_sum[2][wbase + tgt], P.L.z); }
+        }
         alive = false;
       }
     }
 
+    if (STEAL) {
+      __syncwarp();
+      sum = sum + V3f(sh_sum[0][threadIdx.x], sh_sum[1][threadIdx.x], sh_sum[2][threadIdx.x]);
+    }
     if (valid) {
       float4* dst = A.accum + (size_t)py * W.width + px;
       float cnt = (float)(s1 - s0);

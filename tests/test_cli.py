@@ -28,7 +28,8 @@ def test_cli_renders_the_same_image_as_the_library(tmp_path):
     ctx = R.Context(0)
     gs = ctx.scene(s.desc)
     want = ctx.resolve(ctx.render(gs, s.camera, s.integrator, seed=5), 64)
-    assert np.array_equal(img, want)
+    # sample chunks of a tile are summed with float atomics, so two runs can differ in the last bit
+    assert np.abs(img - want.astype(np.int64)).max() <= 1 and (img != want).mean() < 0.01
     gs.close(); ctx.close()
 
 
