@@ -187,3 +187,21 @@ def test_specialised_kernel_instance_equals_the_general_one(ctx, book, scene_no,
     lum_a, lum_b = a[..., :3].sum(axis=2), b[..., :3].sum(axis=2)
     differs = np.abs(lum_a - lum_b) > 1e-3 * np.maximum(lum_b, 1e-3)
     assert differs.mean() < 0.05, differs.mean()
+
+
+@pytest.mark.parametrize("book,scene_no", [("in_one_weekend", None), ("the_next_week", 7), ("the_rest_of_your_life", None)])
+def test_sample_stealing_traces_every_sample_exactly_once(ctx, book, scene_no, monkeypatch):
+    """Lanes that run out of their pixel's samples take over a neighbour's (render_kernel.cuh).  Every
+    (pixel, sample) keeps its own Philox key, so with stealing off (RRT_NO_STEAL) the frame is the
+    same up to float summation order, and .w still counts every sample once."""
+    s = R.BookScene(book, scene_no, overrides=dict(image_width=100, samples_per_pixel=49, max_depth=10))
+    gs = ctx.scene(s.desc)
+    a = ctx.render(gs, s.camera, s.integrator, seed=9).astype(np.float64)
+    monkeypatch.setenv("RRT_NO_STEAL", "1")
+    own = R.Context(0)
+    monkeypatch.delenv("RRT_NO_STEAL")
+    go = own.scene(s.desc)
+    b = own.render(go, s.camera, s.integrator, seed=9).astype(np.float64)
+    go.close(); own.close(); gs.close()
+    assert np.all(a[..., 3] == 49) and np.all(b[..., 3] == 49)
+    assert np.allclose(a[..., :3], b[..., :3], rtol=1e-4, atol=1e-5)
