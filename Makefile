@@ -29,7 +29,7 @@ $(CSRC)/flatten.o: $(CSRC)/flatten.cpp $(CSRC)/flatten.hpp $(CSRC)/device_types.
 
 KOBJ := $(CSRC)/kernels_book1.o $(CSRC)/kernels_book2.o $(CSRC)/kernels_book3.o
 $(PKG)/librrt.so: $(CSRC)/kernels.o $(KOBJ) $(CSRC)/probe64.o $(CSRC)/api.o $(CSRC)/flatten.o
-	$(NVCC) -shared -o $@ $^ -cudart shared
+	$(NVCC) -gencode arch=compute_100a,code=sm_100a -shared -o $@ $^ -cudart shared
 
 HOST_SRC := $(HOST)/books.cpp $(HOST)/rtw_image.cpp $(HOST)/jpeg_decode.cpp $(HOST)/render_io.cpp
 $(PKG)/librrt_host.so: $(HOST_SRC) $(HOST)/*.hpp include/*.h

@@ -18,7 +18,9 @@ template <int ROUNDS>
 __host__ __device__ inline void philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
                                           uint32_t k0, uint32_t k1, uint32_t out[4]) {
   const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#if defined(__CUDA_ARCH__)
 #pragma unroll
+#endif
   for (int r = 0; r < ROUNDS; ++r) {
 #if defined(__CUDA_ARCH__)
     uint32_t hi0 = __umulhi(M0, c0), hi1 = __umulhi(M1, c2);

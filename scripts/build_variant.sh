@@ -15,6 +15,6 @@ nvcc $F -fmad=false "$@" -c $C/probe64.cu -o $tmp/probe64.o &
 nvcc $F --use_fast_math "$@" -c $C/api.cu -o $tmp/api.o &
 nvcc $F --use_fast_math "$@" -x cu -c $C/flatten.cpp -o $tmp/flatten.o &
 wait
-nvcc -shared -o $out/librrt_$name.so $tmp/kernels.o $tmp/kernels_book1.o $tmp/kernels_book2.o $tmp/kernels_book3.o $tmp/probe64.o $tmp/api.o $tmp/flatten.o -cudart shared 
+nvcc -gencode arch=compute_100a,code=sm_100a -shared -o $out/librrt_$name.so $tmp/kernels.o $tmp/kernels_book1.o $tmp/kernels_book2.o $tmp/kernels_book3.o $tmp/probe64.o $tmp/api.o $tmp/flatten.o -cudart shared 
 rm -rf $tmp
 echo built $out/librrt_$name.so
