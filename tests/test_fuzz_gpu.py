@@ -124,3 +124,28 @@ def test_empty_and_single_primitive_worlds(ctx):
     oids, _ = O.OracleScene(d2).probe(cam)
     assert np.array_equal(ids, oids) and (ids == s).any()
     gs2.close()
+
+
+@pytest.mark.parametrize("seed", [1, 2, 5, 8, 13, 21])
+def test_box_leaves_change_nothing_but_the_tree(ctx, seed, monkeypatch):
+    """Axis-aligned boxes become one BVH leaf each (slab test + entry-face quad test, all six quads when
+    that does not settle it).  With the grouping off (RRT_NO_BOX_LEAVES, read by the flattener) the
+    same rays must find the same hits: frames agree up to float summation order, including scenes
+    with glass boxes (rays starting inside a box) and metal ones (rays leaving along a face)."""
+    b, d, cam = random_scene(seed)
+    extra = [box(b, (-3.5 + 2.2 * k, -1.0, 1.0 + 0.3 * k), (-2.0 + 2.2 * k, 0.4 + 0.2 * k, 2.4), k % 5) for k in range(3)]
+    d = b.desc(b.list([d.world] + extra))   # three more boxes: lambertian, metal, glass among them
+    cam = R.copy_camera(cam, image_width=96, samples_per_pixel=64)
+    gs = ctx.scene(d)
+    a = ctx.render(gs, cam, F.INT_BOOK2, seed=seed).astype(np.float64)
+    gs.close()
+    monkeypatch.setenv("RRT_NO_BOX_LEAVES", "1")
+    gq = ctx.scene(d)
+    monkeypatch.delenv("RRT_NO_BOX_LEAVES")
+    q = ctx.render(gq, cam, F.INT_BOOK2, seed=seed).astype(np.float64)
+    gq.close()
+    assert np.array_equal(a[..., 3], q[..., 3])
+    la, lq = a[..., :3].sum(axis=2), q[..., :3].sum(axis=2)
+    differs = np.abs(la - lq) > 1e-4 * np.maximum(lq, 1e-3)
+    assert differs.mean() < 0.002, differs.mean()     # exact edge ties may pick the adjacent face
+    assert np.all(np.abs(a[..., :3].mean(axis=(0, 1)) - q[..., :3].mean(axis=(0, 1))) <= 1e-3 * q[..., :3].mean(axis=(0, 1)))
