@@ -282,7 +282,6 @@ int rrt_render_device(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, co
     chunks = std::max(1LL, std::min(want, cap));
   }
   W.chunks = (int)chunks;
-  W.steal = steal ? 1 : 0;
   W.atomic_accum = chunks > 1 ? 1 : 0;
   A.accum = reinterpret_cast<float4*>(accum_dev);
   A.counter = c->counter;

@@ -162,7 +162,6 @@ struct DevWork {
   int tiles_x;          // 8x4-pixel warp tiles per row
   int n_tiles;          // warp tiles owned by this rank
   int chunks;           // sample chunks per tile
-  int steal;            // lanes take over neighbours' samples once their own pixel is done (render_kernel.cuh)
   int s_begin, s_end;   // sample range of this rank
   int shard_mode, rank, world;
   int stiles_x, stiles_y;   // 32x32 super tiles (tile sharding)

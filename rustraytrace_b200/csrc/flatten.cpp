@@ -305,12 +305,11 @@ struct Walker {
     for (int s = 0; s < 6; ++s) g.member[s] = -1;
     for (int k = 0; k < 6; ++k) {
       const int ax = axis_of[k];
-      const double ext = g.hi[ax] - g.lo[ax], tol = 1e-9 * std::max(1.0, std::fabs(g.hi[ax]) + std::fabs(g.lo[ax]));
+      const double tol = 1e-9 * std::max(1.0, std::fabs(g.hi[ax]) + std::fabs(g.lo[ax]));
       int side;
       if (std::fabs(plane[k] - g.lo[ax]) <= tol) side = 0;
       else if (std::fabs(plane[k] - g.hi[ax]) <= tol) side = 1;
       else return;
-      (void)ext;
       for (int a = 0; a < 3; ++a) {   // the face must span the whole box in its own two axes
         if (a == ax) continue;
         const double t2 = 1e-9 * std::max(1.0, std::fabs(g.hi[a]) + std::fabs(g.lo[a]));
@@ -737,7 +736,6 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
   std::vector<int> leaf_ref(B.nodes.size(), 0);
   {
     // emit prims leaf by leaf in B.order sequence (DFS), reordering within the leaf by kind
-    std::vector<int> first_of(B.nodes.size(), -1);
     int emitted = 0;
     // B.order ranges of leaves are disjoint and cover [0,n); walk nodes, leaves own [first,count)
     std::vector<int> leaves;
