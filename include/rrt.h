@@ -176,7 +176,11 @@ typedef struct rrt_stats {
 typedef struct rrt_ctx rrt_ctx;
 typedef struct rrt_scene rrt_scene;
 
-/* CudaDevice::new(0), src/cuda/mod.rs:343.  One context per process-and-GPU. */
+/* CudaDevice::new(0), src/cuda/mod.rs:343.  One context per process-and-GPU.
+ * Debugging switches read from the environment (results are unchanged up to float summation order):
+ *   RRT_KERNEL=full        (rrt_init) always run the general render-kernel instance
+ *   RRT_NO_STEAL=1         (rrt_init) lanes never take over a neighbour pixel's samples
+ *   RRT_NO_BOX_LEAVES=1    (rrt_scene_create) axis-aligned boxes stay six separate quad leaves */
 int rrt_init(int device, rrt_ctx** out);
 void rrt_shutdown(rrt_ctx* ctx);
 
