@@ -1,7 +1,15 @@
+"""Probe mismatches against the oracle, with the primitives involved:
+    python scripts/probe_debug.py the_next_week 9 200      (scene number "-" for books 1 and 3)"""
+import os
 import sys
+
 import numpy as np
-import oracle_ffi as O
-import rustraytrace_b200 as R
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "tests")]
+import oracle_ffi as O  # noqa: E402
+import rustraytrace_b200 as R  # noqa: E402
+
 book, sc, w = sys.argv[1], (None if sys.argv[2] == "-" else int(sys.argv[2])), int(sys.argv[3])
 s = R.BookScene(book, sc, overrides=dict(image_width=w))
 ctx = R.Context(0)
