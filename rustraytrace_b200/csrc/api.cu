@@ -475,9 +475,11 @@ extern "C" int rrt_flatten_check(const rrt_scene_desc* desc, int32_t* n_prims, i
   const int nn = (int)(F.nodes.size() / 4);
   std::vector<int> seen(F.n_prims, 0);
   std::vector<int> node_seen(nn, 0);
-  auto mark_leaf = [&](int ref) -> bool {
+  auto mark_leaf = [&](int ref, bool is_root) -> bool {
     int leaf = ~ref, first = leaf >> 8, ns = (leaf >> 4) & 15, nq = leaf & 15;
-    if ((leaf & 0xFF) == LEAF_BOX_MARK) {  // box leaf: six quads named by the box record
+    const bool is_box = (leaf & 0xFF) == LEAF_BOX_MARK;
+    if (!is_root && !is_box && ns + nq != 1) return false;  // the traversal loop tests exactly one primitive per leaf
+    if (is_box) {  // box leaf: six quads named by the box record
       if (first < 0 || 2 * first + 1 >= (int)F.boxes.size()) return false;
       first = as_int(F.boxes[2 * first].w); ns = 0; nq = 6;
     }
@@ -486,7 +488,7 @@ extern "C" int rrt_flatten_check(const rrt_scene_desc* desc, int32_t* n_prims, i
     return true;
   };
   if (F.root_ref < 0) {
-    if (!mark_leaf(F.root_ref)) return fail(RRT_ERR_INVALID, "flatten check: root leaf out of range");
+    if (!mark_leaf(F.root_ref, true)) return fail(RRT_ERR_INVALID, "flatten check: root leaf out of range");
   } else {
     struct Item { int node; Box box; bool has_box; };
     std::vector<Item> stack;
@@ -509,7 +511,7 @@ extern "C" int rrt_flatten_check(const rrt_scene_desc* desc, int32_t* n_prims, i
       Box bx[2] = {c0, c1};
       for (int k = 0; k < 2; ++k) {
         if (refs[k] >= 0) { Item ch; ch.node = refs[k]; ch.box = bx[k]; ch.has_box = true; stack.push_back(ch); }
-        else if (!mark_leaf(refs[k])) return fail(RRT_ERR_INVALID, "flatten check: leaf out of range");
+        else if (!mark_leaf(refs[k], false)) return fail(RRT_ERR_INVALID, "flatten check: leaf out of range or not a single primitive");
       }
     }
     for (int i = 0; i < nn; ++i) if (node_seen[i] != 1) return fail(RRT_ERR_INVALID, "flatten check: unreachable node");

@@ -36,8 +36,9 @@ struct FlatScene {
 #define RRT_SINGLE_LEAF_MAX 16
 #endif
 // single_leaf_max: scenes with at most this many primitives become one root leaf (brute force).
+// max_leaf: primitives per leaf below the root; the render kernel's traversal loop relies on 1.
 int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err,
-                  int single_leaf_max = RRT_SINGLE_LEAF_MAX, int max_leaf = 4);
+                  int single_leaf_max = RRT_SINGLE_LEAF_MAX, int max_leaf = 1);
 
 // Camera::initialize (camera.rs:108-154) -> device camera blocks.  Returns image height.
 int camera_initialize(const rrt_camera* cam, DevCamera& c32, DevCamera64& c64);

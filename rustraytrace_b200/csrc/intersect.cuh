@@ -194,6 +194,16 @@ __device__ __forceinline__ void slab2(float4 n0, float4 n1, float4 n2, float idx
   far1 = fminf(fminf(fx.y, fy.y), fminf(fz.y, tmax));
 }
 
+// A leaf below the root holds exactly one primitive (or one box): the flattener builds the tree down
+// to single primitives (flatten.hpp max_leaf = 1), so the traversal loop needs no per-leaf loops.
+template <int FEAT>
+__device__ __forceinline__ void leaf1_hit32(const float4* __restrict__ prims, const float4* __restrict__ boxes, int leaf,
+                                            const Ray32& r, V3f id, float a, float inv_a, float tmin, int skip, bool motion, Hit32& h) {
+  if ((FEAT & SF_BOXES) && (leaf & 0xFF) == LEAF_BOX_MARK) { box_leaf_hit32(prims, boxes, leaf >> 8, r, id, tmin, skip, h); return; }
+  if (!(FEAT & SF_QUADS) || (leaf & 0x10)) sphere_hit32(prims, leaf >> 8, r, a, inv_a, tmin, skip, motion, h);
+  else quad_hit32(prims, leaf >> 8, r, tmin, skip, h);
+}
+
 // World::hit for the render kernel: closest hit in (tmin, +inf).
 // Nodes and primitives come through L1 (ld.global.nc).
 template <int FEAT>
@@ -244,7 +254,7 @@ __device__ inline void world_hit32(const DevScene& S, const Ray32& r, float tmin
     }
     if (done) break;
     if (cur < 0) {
-      leaf_hit32<FEAT>(S.prims, S.boxes, ~cur, r, V3f(idx, idy, idz), a, inv_a, tmin, skip, motion, h);
+      leaf1_hit32<FEAT>(S.prims, S.boxes, ~cur, r, V3f(idx, idy, idz), a, inv_a, tmin, skip, motion, h);
       if (sp == 0) break;
       cur = stack[--sp];
     }
