@@ -48,7 +48,7 @@ __device__ inline float reflectance(float cosine, float ri) {  // material.rs:10
   return r0 + (1.0f - r0) * m2 * m2 * m;
 }
 __device__ inline float clampf(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
-__device__ inline bool finite3(V3f v) { return isfinite(v.x) && isfinite(v.y) && isfinite(v.z); }
+__device__ inline bool finite3(V3f v) { return isfinite(v.x + v.y + v.z); }  // radiance is >= 0: the sum is finite iff all three are
 
 // tile index of this rank -> top-left pixel.  Super tiles are 32x32 pixels = 4x8 warp tiles;
 // super tile k belongs to rank k % world (RRT_SHARD_TILE); otherwise world == 1.

@@ -127,11 +127,10 @@ __device__ inline void make_surface(const DevScene& S, const Ray32& r, const Hit
     s.is_sphere = false;
     s.n_obj = outward;
   } else {
-    float4 p0 = ldg4(rec), p1 = ldg4(rec + 1), m = ldg4(rec + 2);
+    float4 p0 = ldg4(rec), m = ldg4(rec + 2);
     V3f c(p0.x, p0.y, p0.z);
-    if ((FEAT & SF_MOTION) && S.has_motion) c = c + r.tm * V3f(p1.x, p1.y, p1.z);
-    outward = (p - c) * p1.w;                       // (p - center) / radius
-    outward = normalize(outward);
+    if ((FEAT & SF_MOTION) && S.has_motion) { float4 p1 = ldg4(rec + 1); c = c + r.tm * V3f(p1.x, p1.y, p1.z); }
+    outward = normalize(p - c);                     // (p - center) / radius, sphere.rs:93, renormalised in f32
     p = c + p0.w * outward;                         // back onto the sphere
     s.mat = __float_as_int(m.x);
     s.is_sphere = true;
