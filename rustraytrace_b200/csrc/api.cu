@@ -176,6 +176,7 @@ int rrt_scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out) {
   }
   D.texels = texels;
   D.root_ref = F.root_ref;
+  D.front_ref = F.front_ref;
   D.n_nodes = (int)(F.nodes.size() / 4);
   D.n_prims = F.n_prims;
   D.n_media = (int)F.media.size();
@@ -487,6 +488,7 @@ extern "C" int rrt_flatten_check(const rrt_scene_desc* desc, int32_t* n_prims, i
     for (int k = first; k < first + ns + nq; ++k) seen[k]++;
     return true;
   };
+  if (!mark_leaf(F.front_ref, true)) return fail(RRT_ERR_INVALID, "flatten check: front run out of range");
   if (F.root_ref < 0) {
     if (!mark_leaf(F.root_ref, true)) return fail(RRT_ERR_INVALID, "flatten check: root leaf out of range");
   } else {

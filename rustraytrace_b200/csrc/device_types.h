@@ -151,6 +151,7 @@ struct DevScene {
   const DevMedium* media;
   const DevLight* lights;
   int root_ref;
+  int front_ref;     // leaf-format run tested ahead of the traversal (primitives spanning most of the scene); ~0 = none
   int n_nodes, n_prims, n_media, n_lights;
   int has_motion;    // any sphere with dc != 0
   int features;      // SceneFeature bits

@@ -393,7 +393,7 @@ struct Walker {
 // ------------------------------------------------------------------------------------------------
 // BVH: binary, full-sweep SAH over the three axes (host, once per scene).  Not the reference's
 // 12-bucket builder (bvh.rs:34-156) — the closest hit does not depend on the tree.
-enum { ITEM_BOX = 2 };  // build item standing for a BoxGroup (BakedPrim::kind beyond PRIM_SPHERE / PRIM_QUAD)
+enum { ITEM_BOX = 2, FRONT_MAX = 4 };  // build item standing for a BoxGroup (BakedPrim::kind beyond PRIM_SPHERE / PRIM_QUAD)
 
 struct BNode {
   double lo[3], hi[3];
@@ -722,6 +722,30 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
       items.push_back(it); item_src.push_back(-1 - (int)g);
     }
   }
+  // front run: a primitive whose box spans most of the scene (the r = 1000 ground sphere of the
+  // book-1/2 sphere scenes, mod.rs:59-63) sits at the root of any BVH as a leaf of its own, where it
+  // costs every ray a node step and the warp a leaf round of its own.  Such primitives leave the
+  // tree and are tested ahead of the traversal by all lanes together (DevScene::front_ref).
+  int n_front = 0;
+  if (!single && !std::getenv("RRT_NO_FRONT")) {
+    double lo[3], hi[3];
+    for (int a = 0; a < 3; ++a) { lo[a] = std::numeric_limits<double>::infinity(); hi[a] = -lo[a]; }
+    for (const BakedPrim& p : items)
+      for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], p.lo[a]); hi[a] = std::max(hi[a], p.hi[a]); }
+    const double total = Builder::area(lo, hi);
+    std::vector<char> is_front(items.size(), 0);
+    for (size_t i = 0; i < items.size() && n_front < FRONT_MAX; ++i)
+      if (items[i].kind != ITEM_BOX && Builder::area(items[i].lo, items[i].hi) >= 0.5 * total) { is_front[i] = 1; ++n_front; }
+    if (n_front > 0) {  // front items first, construction order kept inside both groups
+      std::vector<BakedPrim> it2; std::vector<int> src2;
+      for (int pass = 1; pass >= 0; --pass)
+        for (size_t i = 0; i < items.size(); ++i)
+          if (is_front[i] == pass) { it2.push_back(items[i]); src2.push_back(item_src[i]); }
+      items.swap(it2); item_src.swap(src2);
+    }
+  }
+  std::vector<BakedPrim> front(items.begin(), items.begin() + n_front);
+  items.erase(items.begin(), items.begin() + n_front);
   Builder B(items, single ? (int)items.size() : max_leaf);
   int root = 0;
   if (single) {
@@ -737,6 +761,14 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
   {
     // emit prims leaf by leaf in B.order sequence (DFS), reordering within the leaf by kind
     int emitted = 0;
+    {
+      int s = 0, q = 0;
+      for (int pass = 0; pass < 2; ++pass)
+        for (const BakedPrim& p : front)
+          if (p.kind == pass) { emit_prim32(p, out.prims); emit_prim64(p, out.prims64); (pass == 0 ? s : q)++; }
+      out.front_ref = make_leaf_ref(0, s, q);
+      emitted = n_front;
+    }
     // B.order ranges of leaves are disjoint and cover [0,n); walk nodes, leaves own [first,count)
     std::vector<int> leaves;
     for (size_t i = 0; i < B.nodes.size(); ++i) if (B.nodes[i].left < 0) leaves.push_back((int)i);

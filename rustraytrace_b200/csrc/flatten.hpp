@@ -25,6 +25,7 @@ struct FlatScene {
   std::vector<DevMedium> media;
   std::vector<DevLight> lights;
   int root_ref = -1;
+  int front_ref = -1;  // leaf-format run of primitives tested ahead of the traversal (none: ~0)
   int n_prims = 0;
   int has_motion = 0;
   int features = 0;   // SceneFeature bits (device_types.h): which render kernel instance the scene needs

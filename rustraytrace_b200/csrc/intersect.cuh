@@ -216,6 +216,8 @@ __device__ inline void world_hit32(const DevScene& S, const Ray32& r, float tmin
     leaf_hit32<FEAT>(S.prims, S.boxes, ~cur, r, V3f(0.0f, 0.0f, 0.0f), a, inv_a, tmin, skip, motion, h);  // a root leaf is never a box leaf
     return;
   }
+  // front run (flatten.cpp): primitives spanning most of the scene, tested by all lanes together
+  if (S.front_ref != -1) leaf_hit32<FEAT>(S.prims, S.boxes, ~S.front_ref, r, V3f(0.0f, 0.0f, 0.0f), a, inv_a, tmin, skip, motion, h);
   const float idx = safe_rcp(r.d.x), idy = safe_rcp(r.d.y), idz = safe_rcp(r.d.z);
   float oodx = r.o.x * idx, oody = r.o.y * idy, oodz = r.o.z * idz;
   asm("" : "+f"(oodx), "+f"(oody), "+f"(oodz));  // opaque: keep in registers, do not rematerialise in the loop
@@ -367,6 +369,7 @@ __device__ inline void leaf_hit64(const DevScene& S, int leaf, V3d o, V3d d, dou
 __device__ inline void world_hit64(const DevScene& S, V3d o, V3d d, double tmin, Hit64& h) {
   int cur = S.root_ref;
   if (cur < 0) { leaf_hit64(S, ~cur, o, d, tmin, h); return; }
+  if (S.front_ref != -1) leaf_hit64(S, ~S.front_ref, o, d, tmin, h);
   const double idx = 1.0 / d.x, idy = 1.0 / d.y, idz = 1.0 / d.z;
   int stack[RRT_STACK];
   int sp = 0;
