@@ -2,6 +2,7 @@
 // very end and is conservative for boxes.
 #include "flatten.hpp"
 
+#include <cstdio>
 #include <cstdlib>
 #include <algorithm>
 #include <cmath>
@@ -722,20 +723,41 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
       items.push_back(it); item_src.push_back(-1 - (int)g);
     }
   }
-  // front run: a primitive whose box spans most of the scene (the r = 1000 ground sphere of the
-  // book-1/2 sphere scenes, mod.rs:59-63) sits at the root of any BVH as a leaf of its own, where it
-  // costs every ray a node step and the warp a leaf round of its own.  Such primitives leave the
-  // tree and are tested ahead of the traversal by all lanes together (DevScene::front_ref).
+  // front run: a primitive far larger than its neighbours (the r = 1000 ground sphere of the book-1/2
+  // sphere scenes, mod.rs:59-63, and their three r = 1 spheres among 480 of r = 0.2) sits high in any
+  // BVH as a leaf of its own and is reached by a large share of the rays, each time costing the warp a
+  // leaf round.  Such primitives leave the tree and are tested ahead of the traversal by all lanes
+  // together (DevScene::front_ref).  Criterion: box area >= 10x the median item's and >= a share of
+  // the bounds of what is left (the surface-area estimate of "hit by a ray that enters the scene"):
+  // 1 % in sphere scenes, where it measured +8-10 % on top of the ground sphere alone (C1, C2, C3a);
+  // 50 % with quads or boxes in the tree, where taking the four largest spheres and the light out of
+  // the book-2 final scene measured 1.6 % slower.  Repeated on what is left, because without the
+  // ground sphere the bounds are those of the rest.  At most FRONT_MAX primitives.
   int n_front = 0;
   if (!single && !std::getenv("RRT_NO_FRONT")) {
-    double lo[3], hi[3];
-    for (int a = 0; a < 3; ++a) { lo[a] = std::numeric_limits<double>::infinity(); hi[a] = -lo[a]; }
-    for (const BakedPrim& p : items)
-      for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], p.lo[a]); hi[a] = std::max(hi[a], p.hi[a]); }
-    const double total = Builder::area(lo, hi);
+    bool spheres_only = true;
+    for (const BakedPrim& p : items) if (p.kind != PRIM_SPHERE) spheres_only = false;
+    const double share = spheres_only ? 0.01 : 0.5;
     std::vector<char> is_front(items.size(), 0);
-    for (size_t i = 0; i < items.size() && n_front < FRONT_MAX; ++i)
-      if (items[i].kind != ITEM_BOX && Builder::area(items[i].lo, items[i].hi) >= 0.5 * total) { is_front[i] = 1; ++n_front; }
+    for (bool again = true; again && n_front < FRONT_MAX;) {
+      again = false;
+      double lo[3], hi[3];
+      for (int a = 0; a < 3; ++a) { lo[a] = std::numeric_limits<double>::infinity(); hi[a] = -lo[a]; }
+      std::vector<double> areas;
+      for (size_t i = 0; i < items.size(); ++i) {
+        if (is_front[i]) continue;
+        areas.push_back(Builder::area(items[i].lo, items[i].hi));
+        for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], items[i].lo[a]); hi[a] = std::max(hi[a], items[i].hi[a]); }
+      }
+      if (areas.size() <= 2) break;
+      const double total = Builder::area(lo, hi);
+      std::nth_element(areas.begin(), areas.begin() + areas.size() / 2, areas.end());
+      const double median = areas[areas.size() / 2];
+      for (size_t i = 0; i < items.size() && n_front < FRONT_MAX; ++i) {
+        const double ar = Builder::area(items[i].lo, items[i].hi);
+        if (!is_front[i] && items[i].kind != ITEM_BOX && ar >= share * total && ar >= 10.0 * median) { is_front[i] = 1; ++n_front; again = true; }
+      }
+    }
     if (n_front > 0) {  // front items first, construction order kept inside both groups
       std::vector<BakedPrim> it2; std::vector<int> src2;
       for (int pass = 1; pass >= 0; --pass)

@@ -119,6 +119,26 @@ def test_axis_aligned_boxes_become_box_leaves(monkeypatch):
         assert not (R.scene_features(c.desc) & F.SF_BOXES)
 
 
+def test_outsized_primitives_leave_the_tree(monkeypatch):
+    """Front run (flatten.cpp): the r = 1000 ground sphere and the three r = 1 spheres of the book-1
+    scene (in_one_weekend/mod.rs:59-63, :93-105) are tested ahead of the traversal instead of sitting
+    in the BVH; the checker still finds every primitive exactly once.  The book-2 final scene has no
+    such outliers (its largest item is 4x the median) and keeps everything in the tree."""
+    s = R.BookScene("in_one_weekend", overrides=dict(image_width=64))
+    front = R.flatten_check(s.desc)
+    monkeypatch.setenv("RRT_NO_FRONT", "1")
+    plain = R.flatten_check(s.desc)
+    monkeypatch.delenv("RRT_NO_FRONT")
+    assert front["n_prims"] == plain["n_prims"]
+    assert plain["n_nodes"] == plain["n_prims"] - 1          # single-primitive leaves: n - 1 inner nodes
+    assert front["n_nodes"] == plain["n_nodes"] - 4          # four primitives left the tree
+    s9 = R.BookScene("the_next_week", 9, overrides=dict(image_width=64))
+    a = R.flatten_check(s9.desc)
+    monkeypatch.setenv("RRT_NO_FRONT", "1")
+    b = R.flatten_check(s9.desc)
+    assert a == b
+
+
 def test_flattener_rejects_malformed_descriptions():
     b = R.DescBuilder()
     m = b.lambertian((0.5, 0.5, 0.5))

@@ -205,3 +205,28 @@ def test_sample_stealing_traces_every_sample_exactly_once(ctx, book, scene_no, m
     go.close(); own.close(); gs.close()
     assert np.all(a[..., 3] == 49) and np.all(b[..., 3] == 49)
     assert np.allclose(a[..., :3], b[..., :3], rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("book,scene_no", [("in_one_weekend", None), ("in_one_weekend_gpu", None), ("the_next_week", 1)])
+def test_front_run_changes_nothing_but_the_tree(ctx, book, scene_no, monkeypatch):
+    """Outsized primitives (the ground sphere, the three r = 1 spheres) are tested ahead of the
+    traversal instead of through the BVH (flatten.cpp front run, read once at rrt_scene_create).  With
+    RRT_NO_FRONT the same rays must find the same hits: probe ids and t identical, frames equal up to
+    float summation order."""
+    s = R.BookScene(book, scene_no, overrides=dict(image_width=160, samples_per_pixel=36, max_depth=12))
+    gs = ctx.scene(s.desc)
+    ids, t = ctx.probe(gs, s.camera, 64)
+    ids32, t32 = ctx.probe(gs, s.camera, 32)
+    a = ctx.render(gs, s.camera, s.integrator, seed=3).astype(np.float64)
+    gs.close()
+    monkeypatch.setenv("RRT_NO_FRONT", "1")
+    gp = ctx.scene(s.desc)
+    monkeypatch.delenv("RRT_NO_FRONT")
+    pids, pt = ctx.probe(gp, s.camera, 64)
+    pids32, pt32 = ctx.probe(gp, s.camera, 32)
+    b = ctx.render(gp, s.camera, s.integrator, seed=3).astype(np.float64)
+    gp.close()
+    assert np.array_equal(ids, pids) and np.array_equal(t, pt)
+    assert np.array_equal(ids32, pids32) and np.array_equal(t32, pt32)
+    assert np.array_equal(a[..., 3], b[..., 3])
+    assert np.allclose(a[..., :3], b[..., :3], rtol=1e-4, atol=1e-5)
