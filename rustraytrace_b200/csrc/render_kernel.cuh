@@ -168,8 +168,14 @@ __device__ __forceinline__ bool shade_step(const DevScene& S, const DevCamera& C
   const bool textured = M.kind == RRT_M_LAMBERTIAN || M.kind == RRT_M_ISOTROPIC || M.kind == RRT_M_DIFFUSE_LIGHT;
   if ((FEAT & SF_TEXTURES) && textured && M.tex >= 0) att = texture_value<FEAT>(S, M.tex, sf.u, sf.v, sf.p);
 
+  // Single exit from here on: a `return` inside the material switch or the roulette test would leave
+  // the lanes that skip it and the lanes that survive it in separate groups for the rest of the
+  // function (ptxas only re-converges single-exit regions), and the mixture-PDF code below then ran
+  // 1.7 times per call at 8.6 lanes on the book-3 scene (profiles/README.md, r01j).  `ok` carries the
+  // reference's early returns instead.
   V3f dir(0.0f, 0.0f, 0.0f);
   bool pdf_branch = false;
+  bool ok = true;
   switch (M.kind) {
     case RRT_M_LAMBERTIAN:
       if (INTEGRATOR == RRT_INT_BOOK3) {
@@ -181,7 +187,7 @@ __device__ __forceinline__ bool shade_step(const DevScene& S, const DevCamera& C
       break;
     case RRT_M_METAL: {  // material.rs:84-96 / the_next_week/material.rs:66-77
       dir = normalize(reflect(ray.d, sf.n)) + M.fuzz * uniform_sphere(ra.x, ra.y);
-      if (INTEGRATOR != RRT_INT_BOOK3 && !(dot(dir, sf.n) > 0.0f)) return false;
+      if (INTEGRATOR != RRT_INT_BOOK3 && !(dot(dir, sf.n) > 0.0f)) ok = false;
       break;
     }
     case RRT_M_DIELECTRIC: {  // material.rs:113-137
@@ -202,52 +208,58 @@ __device__ __forceinline__ bool shade_step(const DevScene& S, const DevCamera& C
       // emitted: book 2 both faces (material.rs:131-135), book 3 front face only (:155-160);
       // book 1 has no emission
       if (INTEGRATOR == RRT_INT_BOOK2 || (INTEGRATOR == RRT_INT_BOOK3 && sf.front)) L = L + T * att;
-      return false;
+      ok = false;
+      break;
     default:
-      return false;  // EmptyMaterial
+      ok = false;  // EmptyMaterial
+      break;
   }
 
   // Russian roulette after five bounces on the local attenuation (camera.rs:200-207, 223-237)
-  float rr = 1.0f;
-  if (bounce >= 5) {
-    rr = clampf(max3(att), 0.05f, 0.95f);
-    if (ra.z > rr) return false;
-  }
-  if (pdf_branch) {
-    // MixturePdf(HittablePdf(lights, p), srec.pdf), camera.rs:239-253, pdf.rs:77-100
-    // one Philox block per bounce: ra.x is the mixture coin, and its remaining mantissa bits
-    // (2 ra.x mod 1, uniform and independent of the coin) pick the light; ra.y, ra.w give the
-    // direction; ra.z is the roulette draw above; ra.v the medium's free-flight draw
-    const bool lamb = M.kind == RRT_M_LAMBERTIAN;
-    const int nl = S.n_lights;
-    const bool pick_light = ra.x < 0.5f;
-    const float u_pick = 2.0f * ra.x - (pick_light ? 0.0f : 1.0f);
-    if (nl > 0 && pick_light) {
-      int li = min((int)(u_pick * (float)nl), nl - 1);  // random_int(0, n-1), hittable_list.rs:71-75
-      dir = light_random(S.lights[li], sf.p, ra.y, ra.w);
-    } else if (lamb) {
-      dir = Onb(sf.n).transform(cosine_direction(ra.y, ra.w));  // pdf.rs:51-53
+  const float rrc = clampf(max3(att), 0.05f, 0.95f);
+  const bool deep = bounce >= 5;
+  const float rr = deep ? rrc : 1.0f;
+  if (deep && ra.z > rrc) ok = false;
+  if (ok) {
+    if (pdf_branch) {
+      // MixturePdf(HittablePdf(lights, p), srec.pdf), camera.rs:239-253, pdf.rs:77-100
+      // one Philox block per bounce: ra.x is the mixture coin, and its remaining mantissa bits
+      // (2 ra.x mod 1, uniform and independent of the coin) pick the light; ra.y, ra.w give the
+      // direction; ra.z is the roulette draw above; ra.v the medium's free-flight draw
+      const bool lamb = M.kind == RRT_M_LAMBERTIAN;
+      const int nl = S.n_lights;
+      const bool pick_light = ra.x < 0.5f;
+      const float u_pick = 2.0f * ra.x - (pick_light ? 0.0f : 1.0f);
+      if (nl > 0 && pick_light) {
+        int li = min((int)(u_pick * (float)nl), nl - 1);  // random_int(0, n-1), hittable_list.rs:71-75
+        dir = light_random(S.lights[li], sf.p, ra.y, ra.w);
+      } else if (lamb) {
+        dir = Onb(sf.n).transform(cosine_direction(ra.y, ra.w));  // pdf.rs:51-53
+      } else {
+        dir = uniform_sphere(ra.y, ra.w);  // SpherePdf, pdf.rs:27-29
+      }
+      V3f udir = normalize(dir);
+      float cos_n = dot(sf.n, udir);
+      float pdf_mat = lamb ? (cos_n > 0.0f ? cos_n * (1.0f / RRT_PI) : 0.0f) : (0.25f / RRT_PI);
+      float pdf_value = pdf_mat;
+      if (nl > 0) {
+        float pl = 0.0f;
+        for (int i = 0; i < nl; ++i) pl += light_pdf(S.lights[i], sf.p, dir);  // hittable_list.rs:60-69
+        pdf_value = 0.5f * (pl / (float)nl) + 0.5f * pdf_mat;
+      }
+      ok = pdf_value > 0.0f;  // camera.rs:243-246
+      float spdf = lamb ? (cos_n < 0.0f ? 0.0f : cos_n * (1.0f / RRT_PI)) : (0.25f / RRT_PI);  // material.rs:63-70, 186-188
+      if (ok) T = T * (att * (spdf / (pdf_value * rr)));
     } else {
-      dir = uniform_sphere(ra.y, ra.w);  // SpherePdf, pdf.rs:27-29
+      T = T * (att * (1.0f / rr));
     }
-    V3f udir = normalize(dir);
-    float cos_n = dot(sf.n, udir);
-    float pdf_mat = lamb ? (cos_n > 0.0f ? cos_n * (1.0f / RRT_PI) : 0.0f) : (0.25f / RRT_PI);
-    float pdf_value = pdf_mat;
-    if (nl > 0) {
-      float pl = 0.0f;
-      for (int i = 0; i < nl; ++i) pl += light_pdf(S.lights[i], sf.p, dir);  // hittable_list.rs:60-69
-      pdf_value = 0.5f * (pl / (float)nl) + 0.5f * pdf_mat;
-    }
-    if (!(pdf_value > 0.0f)) return false;  // camera.rs:243-246
-    float spdf = lamb ? (cos_n < 0.0f ? 0.0f : cos_n * (1.0f / RRT_PI)) : (0.25f / RRT_PI);  // material.rs:63-70, 186-188
-    T = T * (att * (spdf / (pdf_value * rr)));
-  } else {
-    T = T * (att * (1.0f / rr));
   }
-  ray.o = sf.p; ray.d = dir;
-  P.bounce = bounce + 1;
-  return P.bounce < max_depth;  // depth <= 0 -> black, camera.rs:185-187
+  if (ok) {
+    ray.o = sf.p; ray.d = dir;
+    P.bounce = bounce + 1;
+    ok = P.bounce < max_depth;  // depth <= 0 -> black, camera.rs:185-187
+  }
+  return ok;
 }
 
 // ---- the megakernel ---------------------------------------------------------------------------------
