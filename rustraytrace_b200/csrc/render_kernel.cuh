@@ -230,13 +230,33 @@ __device__ __forceinline__ bool shade_step(const DevScene& S, const DevCamera& C
       const int nl = S.n_lights;
       const bool pick_light = ra.x < 0.5f;
       const float u_pick = 2.0f * ra.x - (pick_light ? 0.0f : 1.0f);
+      // The cosine lobe about the normal (pdf.rs:51-53, vec3.rs:212-222) and the cone towards a sphere
+      // light (sphere.rs:55-65, 117-122) are the same code around different axes and heights z: one
+      // basis, one sincos and one transform for both groups of lanes instead of a branch each.
+      V3f axis = sf.n;
+      float z = 0.0f;
+      bool around_axis = true;
       if (nl > 0 && pick_light) {
-        int li = min((int)(u_pick * (float)nl), nl - 1);  // random_int(0, n-1), hittable_list.rs:71-75
-        dir = light_random(S.lights[li], sf.p, ra.y, ra.w);
+        const int li = min((int)(u_pick * (float)nl), nl - 1);  // random_int(0, n-1), hittable_list.rs:71-75
+        const DevLight& Lt = S.lights[li];
+        if (Lt.kind == 0) {
+          axis = V3f(Lt.a.x, Lt.a.y, Lt.a.z) - sf.p;
+          z = 1.0f + ra.w * (sqrtf(fmaxf(0.0f, 1.0f - Lt.a.w * Lt.a.w / dot(axis, axis))) - 1.0f);
+        } else {
+          dir = light_random(Lt, sf.p, ra.y, ra.w);  // quad light, or the trait default
+          around_axis = false;
+        }
       } else if (lamb) {
-        dir = Onb(sf.n).transform(cosine_direction(ra.y, ra.w));  // pdf.rs:51-53
+        z = sqrtf(fmaxf(0.0f, 1.0f - ra.w));
       } else {
         dir = uniform_sphere(ra.y, ra.w);  // SpherePdf, pdf.rs:27-29
+        around_axis = false;
+      }
+      if (around_axis) {
+        float sn, cs;
+        __sincosf(2.0f * RRT_PI * ra.y - RRT_PI, &sn, &cs);
+        const float q = sqrtf(fmaxf(0.0f, 1.0f - z * z));
+        dir = Onb(axis).transform(V3f(cs * q, sn * q, z));
       }
       V3f udir = normalize(dir);
       float cos_n = dot(sf.n, udir);
