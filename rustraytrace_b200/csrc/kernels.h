@@ -27,16 +27,22 @@ struct ProbeArgs {
 
 // Resident CTAs per SM each render kernel instance is compiled for (its register budget).  Every
 // instance without Perlin noise fits 64 registers spill-free: 8 CTAs, 32 warps per SM.  The
-// turbulence loop (7 octaves of 8 gradient lookups) pushes an instance to 80 registers (6 CTAs);
-// 72 or 64 registers spill 100-170 bytes there and measured within 1 % (profiles/README.md).
+// turbulence loop (7 octaves of 8 gradient lookups) pushes an instance to 80 registers (6 CTAs).
+// The noise instances that also carry media (the book-2 final scene) run 7 CTAs at 72 registers with
+// the same 40 bytes of spills they have at 80: C4 +3.5 %; the plain noise instances lose 2 % there
+// (C3c) and stay at 6; 64 registers spills 110-180 bytes, and a rolled corner loop in perlin_noise
+// does not remove that and costs C3c 57 % (profiles/README.md, r01j).
 #ifndef RRT_MIN_BLOCKS_LEAN
 #define RRT_MIN_BLOCKS_LEAN 8
 #endif
 #ifndef RRT_MIN_BLOCKS
 #define RRT_MIN_BLOCKS 6
 #endif
+#ifndef RRT_MIN_BLOCKS_NOISE_MEDIA
+#define RRT_MIN_BLOCKS_NOISE_MEDIA 7
+#endif
 constexpr int render_min_blocks(int feat) {
-  return (feat & SF_NOISE) ? RRT_MIN_BLOCKS : RRT_MIN_BLOCKS_LEAN;
+  return (feat & SF_NOISE) ? ((feat & SF_MEDIA) ? RRT_MIN_BLOCKS_NOISE_MEDIA : RRT_MIN_BLOCKS) : RRT_MIN_BLOCKS_LEAN;
 }
 
 // One compiled instance of render_kernel<INTEGRATOR, FEAT> (kernels_book{1,2,3}.cu).

@@ -17,12 +17,14 @@ iA, iS, iI, iT = hdr.index("Address"), hdr.index("Source"), hdr.index("Instructi
 data = [r for r in rows[2:] if len(r) > iT]
 base = int(data[0][iA], 16)
 tot = sum(int(r[iI]) for r in data)
-# one segment = one execution of the three reciprocals of the ray direction (safe_rcp x3) or, for
-# root-leaf scenes, of the a = dot(d, d) reciprocal: take the most frequent MUFU.RCP count at >= 20 lanes
-seg = None
+# one segment = one world_hit32 call: the most frequent execution count among the instructions that
+# run with (nearly) all lanes of the warp (ray set-up, Philox block, hit record): the mode
+from collections import Counter
+mode = Counter()
 for r in data:
-    if "MUFU.RCP" in r[iS] and int(r[iI]) and int(r[iT]) / int(r[iI]) >= 20:
-        seg = int(r[iI]) if seg is None else min(seg, int(r[iI]))
+    if int(r[iI]) and int(r[iT]) / int(r[iI]) >= 20:
+        mode[int(r[iI])] += int(r[iI])   # weighted by executions, so the once-per-work-item prologue does not win
+seg = mode.most_common(1)[0][0]
 print(f"warp instructions {tot:.4g}; segment (world_hit32 call) count {seg:.4g}; {tot / seg:.0f} warp instructions per segment")
 groups = []
 for r in data:
