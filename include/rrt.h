@@ -180,7 +180,9 @@ typedef struct rrt_scene rrt_scene;
  * Debugging switches read from the environment (results are unchanged up to float summation order):
  *   RRT_KERNEL=full        (rrt_init) always run the general render-kernel instance
  *   RRT_NO_STEAL=1         (rrt_init) lanes never take over a neighbour pixel's samples
- *   RRT_NO_BOX_LEAVES=1    (rrt_scene_create) axis-aligned boxes stay six separate quad leaves */
+ *   RRT_NO_BOX_LEAVES=1    (rrt_scene_create) axis-aligned boxes stay six separate quad leaves
+ *   RRT_NO_FRONT=1         (rrt_scene_create) outsized primitives (a ground sphere) stay in the BVH instead of
+ *                          being tested ahead of the traversal */
 int rrt_init(int device, rrt_ctx** out);
 void rrt_shutdown(rrt_ctx* ctx);
 
