@@ -35,6 +35,24 @@ def test_random_scene_graph_flattens_to_a_valid_bvh(seed):
         assert not (feat & F.SF_BOXES)                   # small scenes are one brute-force leaf
 
 
+@pytest.mark.parametrize("seed", range(16))
+def test_outsized_primitives_leave_the_tree_and_the_check_still_holds(seed, monkeypatch):
+    """Front run (flatten.cpp): scenes with a ground quad or sphere and a few large spheres among many
+    small primitives.  At most four primitives leave the tree, the self-check (every primitive reached
+    exactly once) holds with and without it, and the primitive count does not change."""
+    g = _generator()
+    b, d, cam = g.outsized_scene(seed)
+    front = R.flatten_check(d)
+    monkeypatch.setenv("RRT_NO_FRONT", "1")
+    plain = R.flatten_check(d)
+    monkeypatch.delenv("RRT_NO_FRONT")
+    assert front["n_prims"] == plain["n_prims"]
+    assert plain["n_nodes"] == plain["n_prims"] - 1
+    assert 1 <= plain["n_nodes"] - front["n_nodes"] <= 4
+    if seed % 2 == 1:   # quads in the tree: only the ground quad (>= 50 % of the bounds) qualifies
+        assert plain["n_nodes"] - front["n_nodes"] == 1
+
+
 def test_box_detection_needs_exactly_the_six_faces(monkeypatch):
     g = _generator()
 

@@ -93,6 +93,64 @@ def test_random_scene_probe_parity(ctx, seed):
     gs.close()
 
 
+def outsized_scene(seed):
+    """Many small primitives and a few far larger ones (a ground quad or sphere, a few big spheres):
+    what the flattener's front run takes out of the BVH (flatten.cpp)."""
+    rng = np.random.default_rng(1000 + seed)
+    b = R.DescBuilder()
+    mats = [b.lambertian(tuple(rng.uniform(0.2, 0.9, 3))) for _ in range(3)]
+    mats.append(b.material(F.M_METAL, albedo=(0.8, 0.8, 0.8), fuzz=0.1))
+    mats.append(b.material(F.M_DIELECTRIC, ri=1.5))
+    pick = lambda: mats[rng.integers(len(mats))]
+    top = []
+    with_quads = seed % 2 == 1
+    for _ in range(int(rng.integers(24, 60))):
+        c = (float(rng.uniform(-6, 6)), float(rng.uniform(0.1, 0.6)), float(rng.uniform(-6, 6)))
+        if with_quads and rng.integers(3) == 0:
+            top.append(b.quad(c, tuple(rng.uniform(-0.4, 0.4, 3)), tuple(rng.uniform(-0.4, 0.4, 3)), pick()))
+        else:
+            top.append(b.sphere(c, float(rng.uniform(0.08, 0.3)), pick()))
+    if with_quads:   # a ground quad spanning far more than half of the bounds
+        top.insert(int(rng.integers(len(top))), b.quad((-500.0, 0.0, -500.0), (1000.0, 0, 0), (0, 0, 1000.0), pick()))
+    else:            # the book-1 ground sphere and a few large spheres among the small ones
+        top.insert(int(rng.integers(len(top))), b.sphere((0.0, -1000.0, 0.0), 1000.0, pick()))
+        for k in range(int(rng.integers(1, 6))):
+            top.insert(int(rng.integers(len(top))), b.sphere((float(rng.uniform(-5, 5)), 1.0, float(rng.uniform(-5, 5))), float(rng.uniform(0.9, 1.6)), pick()))
+    world = b.bvh(top) if rng.integers(2) else b.list(top)
+    cam = R.make_camera(image_width=160, aspect_ratio=1.0, samples_per_pixel=64, max_depth=8, background=(0.6, 0.7, 0.9),
+                        vfov=float(rng.uniform(30, 60)), lookfrom=(float(rng.uniform(-3, 3)), float(rng.uniform(1.5, 4)), 12.0),
+                        lookat=(0.0, 0.5, 0.0))
+    return b, b.desc(world), cam
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_outsized_primitives_probe_parity_and_front_equivalence(ctx, seed, monkeypatch):
+    """Front run against the oracle's pointer-tree BVH (ids bit-exact, t within 1e-5), and against
+    the same scene with every primitive kept in the tree (RRT_NO_FRONT): same hits, same frame."""
+    b, d, cam = outsized_scene(seed)
+    assert R.flatten_check(d)["n_nodes"] < R.flatten_check(d)["n_prims"] - 1   # something left the tree
+    gs = ctx.scene(d)
+    ids, t = ctx.probe(gs, cam, 64)
+    oids, ot = O.OracleScene(d).probe(cam)
+    assert np.array_equal(ids, oids), f"seed {seed}: {(ids != oids).sum()} ids differ"
+    hit = oids >= 0
+    assert hit.any() and np.max(np.abs(t[hit] - ot[hit]) / ot[hit]) <= 1e-5
+    cam2 = R.copy_camera(cam, image_width=96, samples_per_pixel=32)
+    a = ctx.render(gs, cam2, F.INT_BOOK2, seed=seed).astype(np.float64)
+    gs.close()
+    monkeypatch.setenv("RRT_NO_FRONT", "1")
+    gp = ctx.scene(d)
+    monkeypatch.delenv("RRT_NO_FRONT")
+    pids, pt = ctx.probe(gp, cam, 64)
+    q = ctx.render(gp, cam2, F.INT_BOOK2, seed=seed).astype(np.float64)
+    gp.close()
+    assert np.array_equal(ids, pids) and np.array_equal(t, pt)
+    assert np.array_equal(a[..., 3], q[..., 3])
+    la, lq = a[..., :3].sum(axis=2), q[..., :3].sum(axis=2)
+    differs = np.abs(la - lq) > 1e-4 * np.maximum(lq, 1e-3)
+    assert differs.mean() < 0.002, differs.mean()
+
+
 @pytest.mark.parametrize("seed", [3, 7, 11, 19])
 def test_random_scene_render_mean(ctx, seed):
     b, d, cam = random_scene(seed)
