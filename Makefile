@@ -42,8 +42,14 @@ $(PKG)/bin/rrt: $(HOST)/main.cpp $(PKG)/librrt.so $(PKG)/librrt_host.so
 oracle:
 	$(MAKE) -C oracle
 
+# CPU model of the warp-level traversal cost (scripts/warp_sim.cpp; not part of `all`, not shipped):
+#   make warp_sim [SIMFLAGS="-DRRT_FRONT_MAX=8"] && build/warp_sim 1 -1 1200
+warp_sim: $(PKG)/librrt_host.so
+	mkdir -p build
+	$(CXX) -O2 -std=c++17 $(SIMFLAGS) -I$(CSRC) scripts/warp_sim.cpp $(CSRC)/flatten.cpp -L$(PKG) -lrrt_host -Wl,-rpath,$(CURDIR)/$(PKG) -o build/warp_sim
+
 clean:
 	rm -f $(CSRC)/*.o $(PKG)/*.so $(PKG)/bin/rrt
 	$(MAKE) -C oracle clean
 
-.PHONY: all oracle clean
+.PHONY: all oracle clean warp_sim

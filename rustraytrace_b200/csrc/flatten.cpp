@@ -394,7 +394,24 @@ struct Walker {
 // ------------------------------------------------------------------------------------------------
 // BVH: binary, full-sweep SAH over the three axes (host, once per scene).  Not the reference's
 // 12-bucket builder (bvh.rs:34-156) — the closest hit does not depend on the tree.
-enum { ITEM_BOX = 2, FRONT_MAX = 4 };  // build item standing for a BoxGroup (BakedPrim::kind beyond PRIM_SPHERE / PRIM_QUAD)
+// Tree-shape constants; overridable at build time by scripts/warp_sim.cpp (the CPU model of the
+// warp-level traversal cost), which compiles this file with other values to compare trees.
+#ifndef RRT_SAH_NODE_COST
+#define RRT_SAH_NODE_COST 0.3            // price of a node step against one primitive test
+#endif
+#ifndef RRT_FRONT_MAX
+#define RRT_FRONT_MAX 4                  // primitives the front run may hold
+#endif
+#ifndef RRT_FRONT_SHARE_SPHERES
+#define RRT_FRONT_SHARE_SPHERES 0.01     // box-area share of the remaining bounds, sphere-only scenes
+#endif
+#ifndef RRT_FRONT_SHARE_OTHER
+#define RRT_FRONT_SHARE_OTHER 0.5        // the same with quads or boxes in the tree
+#endif
+#ifndef RRT_FRONT_MEDIAN_FACTOR
+#define RRT_FRONT_MEDIAN_FACTOR 10.0     // and at least this many times the median item's box area
+#endif
+enum { ITEM_BOX = 2, FRONT_MAX = RRT_FRONT_MAX };  // build item standing for a BoxGroup (BakedPrim::kind beyond PRIM_SPHERE / PRIM_QUAD)
 
 struct BNode {
   double lo[3], hi[3];
@@ -475,7 +492,7 @@ struct Builder {
     if (best_axis >= 0 && parent_area > 0) {
       // a leaf round costs the whole warp a reconvergence, so a node step is priced well below one
       // intersection: single-primitive leaves measured 1-2 % faster than SAH's usual 1.0 (profiles/README.md)
-      double split_cost = 0.3 + best_cost / parent_area;
+      double split_cost = RRT_SAH_NODE_COST + best_cost / parent_area;
       if (can_leaf && (double)count <= split_cost) return me;
     } else if (can_leaf) {
       return me;
@@ -737,7 +754,7 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
   if (!single && !std::getenv("RRT_NO_FRONT")) {
     bool spheres_only = true;
     for (const BakedPrim& p : items) if (p.kind != PRIM_SPHERE) spheres_only = false;
-    const double share = spheres_only ? 0.01 : 0.5;
+    const double share = spheres_only ? RRT_FRONT_SHARE_SPHERES : RRT_FRONT_SHARE_OTHER;
     std::vector<char> is_front(items.size(), 0);
     for (bool again = true; again && n_front < FRONT_MAX;) {
       again = false;
@@ -755,7 +772,7 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
       const double median = areas[areas.size() / 2];
       for (size_t i = 0; i < items.size() && n_front < FRONT_MAX; ++i) {
         const double ar = Builder::area(items[i].lo, items[i].hi);
-        if (!is_front[i] && items[i].kind != ITEM_BOX && ar >= share * total && ar >= 10.0 * median) { is_front[i] = 1; ++n_front; again = true; }
+        if (!is_front[i] && items[i].kind != ITEM_BOX && ar >= share * total && ar >= RRT_FRONT_MEDIAN_FACTOR * median) { is_front[i] = 1; ++n_front; again = true; }
       }
     }
     if (n_front > 0) {  // front items first, construction order kept inside both groups
