@@ -14,7 +14,8 @@
 //   build/warp_sim <book 1|2|3|4> <scene_no|-1> <image_width> [tiles=1500] [samples_per_lane=8]
 //   RRT_NO_FRONT=1 build/warp_sim 1 -1 1200       # the same rays against the tree without a front run
 // Scheduling variants (environment): SIM_NO_CHAIN / SIM_CHAIN (consecutive leaves in one round off / on),
-// SIM_DEFER=k (a lane puts k leaves aside before it waits), SIM_MAX_LEAF, SIM_SINGLE_LEAF_MAX.
+// SIM_DEFER=k (a lane puts k leaves aside before it waits), SIM_MAX_LEAF, SIM_SINGLE_LEAF_MAX,
+// SIM_TILE=WxH (pixels of a warp's tile), SIM_REGEN_MIN=k (dead lanes start new paths k at a time).
 //
 // Not part of the product and not an oracle: sphere/quad hits and the three book-1 materials in f32,
 // no textures (albedo from the material record), no media, no light sampling.  Validation against the
@@ -307,8 +308,14 @@ int main(int argc, char** argv) {
   // ---- paths, grouped as the kernel groups them -------------------------------------------------
   std::vector<Iter> iters;
   Rng pick(7);
-  const int tiles_x = (C.W + 7) / 8, tiles_y = (C.H + 3) / 4;
+  // tile of a warp: SIM_TILE=WxH pixels with W*H <= 32 (the kernel: 8x4, lane = pixel); smaller tiles put
+  // several lanes on one pixel, each tile pixel then gets 32/(W*H) times the samples
+  int TW = 8, TH = 4;
+  if (const char* e = std::getenv("SIM_TILE")) std::sscanf(e, "%dx%d", &TW, &TH);
+  const int NP = TW * TH, spp_pixel = spl * 32 / NP;
+  const int tiles_x = (C.W + TW - 1) / TW, tiles_y = (C.H + TH - 1) / TH;
   double n_paths = 0, n_segs = 0;
+  const int regen_min = std::getenv("SIM_REGEN_MIN") ? std::atoi(std::getenv("SIM_REGEN_MIN")) : 1;
   for (int t = 0; t < n_tiles; ++t) {
     const int tx = (int)(pick.next() % tiles_x), ty = (int)(pick.next() % tiles_y);
     int next_sample[32], tgt[32], bounce[32], skip_id[32];
@@ -317,20 +324,24 @@ int main(int argc, char** argv) {
     std::vector<Rng> g;
     for (int l = 0; l < 32; ++l) {
       g.emplace_back((uint64_t)t * 64 + l);
-      const int px = tx * 8 + (l & 7), py = ty * 4 + (l >> 3);
-      next_sample[l] = (px < C.W && py < C.H) ? 0 : spl;
-      tgt[l] = l; alive[l] = false; bounce[l] = 0; skip_id[l] = -1;
+      const int px = tx * TW + (l % NP) % TW, py = ty * TH + (l % NP) / TW;
+      next_sample[l] = (l < NP && px < C.W && py < C.H) ? 0 : spp_pixel;
+      tgt[l] = l % NP; alive[l] = false; bounce[l] = 0; skip_id[l] = -1;
     }
     for (;;) {
       Iter it;
       bool any = false;
+      int n_dead = 0;
+      for (int l = 0; l < 32; ++l) n_dead += !alive[l];
+      const bool regen = n_dead >= regen_min || n_dead == 32;   // SIM_REGEN_MIN: dead lanes wait until that many can start together
       for (int l = 0; l < 32; ++l) {
+        if (!alive[l] && !regen) continue;
         if (!alive[l]) {  // next sample of its own pixel, then of a neighbour's (sample stealing)
           int tries = 0;
-          for (; tries < 32; ++tries) { if (next_sample[tgt[l]] < spl) break; tgt[l] = (tgt[l] + 1) & 31; }
-          if (tries == 32) continue;
+          for (; tries < NP; ++tries) { if (next_sample[tgt[l]] < spp_pixel) break; tgt[l] = (tgt[l] + 1) % NP; }
+          if (tries == NP) continue;
           ++next_sample[tgt[l]];
-          const int px = tx * 8 + (tgt[l] & 7), py = ty * 4 + (tgt[l] >> 3);
+          const int px = tx * TW + tgt[l] % TW, py = ty * TH + tgt[l] / TW;
           const float fx = px + g[l].u() - 0.5f, fy = py + g[l].u() - 0.5f;
           V3 rel = C.p00 + fx * C.du + fy * C.dv, o = C.c;
           if (C.defocus) {
@@ -395,6 +406,7 @@ int main(int argc, char** argv) {
               book, scene_no, width, T.F.n_prims, T.F.nodes.size() / 4, (int)(front / ni + 0.5), (int)T.chain, n_paths, n_segs / n_paths, lanes / ni);
   std::printf("per warp and segment: %.2f node steps (%.2f per lane, %.0f %%), %.2f rounds, %.2f leaf rounds, %.2f leaf tests per lane | modelled %.0f warp instructions\n",
               warp_steps / ni, lane_steps / lanes, 100.0 * (lane_steps / lanes) / (warp_steps / ni), rounds / ni, leaf_rounds / ni, lane_leaves / lanes, cost / ni);
+  std::printf("modelled warp instructions per path: %.1f\n", cost / n_paths);
   std::printf("longest lane of a segment: %.2f node steps: of the warp's %.2f, %.2f are the spread between lanes and %.2f the waits at leaf rounds\n",
               longest / ni, warp_steps / ni, longest / ni - lane_steps / lanes, (warp_steps - longest) / ni);
   rrth_scene_free(sc);
