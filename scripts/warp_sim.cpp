@@ -139,7 +139,7 @@ Hit world_hit(const Tree& T, const Ray& r, float tmin, int skip, Trace* tr) {
   const float id[3] = {rcp(r.d.x), rcp(r.d.y), rcp(r.d.z)};
   const float oo[3] = {r.o.x * id[0], r.o.y * id[1], r.o.z * id[2]};
   int stack[64], sp = 0;
-  auto count = [](int ref) { const int lf = ~ref; return (lf & 0xFF) == LEAF_BOX_MARK ? 2 : ((lf >> 4) & 15) + (lf & 15); };  // primitives tested (a box leaf ~ 2)
+  auto count = [](int ref) { const int lf = ~ref; return (lf & 0xFF) == LEAF_BOX_MARK ? 3 : ((lf >> 4) & 15) + (lf & 15); };  // primitives tested (a box leaf ~ 3: slab test, entry face, fall-back)
   for (;;) {
     bool done = false;
     int steps = 0, leaves = 0, buf[8], nb = 0;
@@ -315,6 +315,8 @@ int main(int argc, char** argv) {
   const int NP = TW * TH, spp_pixel = spl * 32 / NP;
   const int tiles_x = (C.W + TW - 1) / TW, tiles_y = (C.H + TH - 1) / TH;
   double n_paths = 0, n_segs = 0;
+  // the kernel takes over neighbours' samples except in the Perlin instances and scenes of <= 2 primitives
+  const bool steal = !std::getenv("SIM_NO_STEAL") && !(T.F.features & SF_NOISE) && T.F.n_prims > 2;
   const int regen_min = std::getenv("SIM_REGEN_MIN") ? std::atoi(std::getenv("SIM_REGEN_MIN")) : 1;
   for (int t = 0; t < n_tiles; ++t) {
     const int tx = (int)(pick.next() % tiles_x), ty = (int)(pick.next() % tiles_y);
@@ -338,7 +340,8 @@ int main(int argc, char** argv) {
         if (!alive[l] && !regen) continue;
         if (!alive[l]) {  // next sample of its own pixel, then of a neighbour's (sample stealing)
           int tries = 0;
-          for (; tries < NP; ++tries) { if (next_sample[tgt[l]] < spp_pixel) break; tgt[l] = (tgt[l] + 1) % NP; }
+          for (; tries < (steal ? NP : 1); ++tries) { if (next_sample[tgt[l]] < spp_pixel) break; tgt[l] = (tgt[l] + 1) % NP; }
+          if (!steal && next_sample[tgt[l]] >= spp_pixel) continue;
           if (tries == NP) continue;
           ++next_sample[tgt[l]];
           const int px = tx * TW + tgt[l] % TW, py = ty * TH + tgt[l] / TW;
@@ -369,7 +372,10 @@ int main(int argc, char** argv) {
 
   // ---- score the tree under test -----------------------------------------------------------------
   // instruction counts per event, from the SASS profile of the r01j kernel (profiles/groups_r01j.txt)
-  const double C_NODE = 43, C_LEAF_ROUND = 12, C_LEAF = 34, C_FRONT = 23, C_SETUP = 45, C_FIXED = 445;
+  // the fixed part of a segment: ray set-up, Philox, shading, regeneration (C2 445); media add two boundary
+  // tests per medium and the free-flight draw, the noise instance its texture code (C4: ~1000 in all)
+  const double C_NODE = 43, C_LEAF_ROUND = 12, C_LEAF = 34, C_FRONT = 23, C_SETUP = 45;
+  const double C_FIXED = 445 + 130.0 * T.F.media.size() + ((T.F.features & SF_NOISE) ? 200 : 0) + ((T.F.features & SF_TEXTURES) ? 60 : 0);
   double longest = 0, warp_steps = 0, lane_steps = 0, rounds = 0, leaf_rounds = 0, lane_leaves = 0, lanes = 0, cost = 0, front = 0;
   Trace tr;
   std::vector<Trace> lane_tr;
