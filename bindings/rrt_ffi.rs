@@ -54,6 +54,12 @@ extern "C" {
                              n_media: *mut i32, n_lights: *mut i32) -> c_int;
     pub fn rrt_scene_features(desc: *const RrtSceneDesc, features: *mut i32) -> c_int;
     pub fn rrt_philox_kat(c0: u32, c1: u32, c2: u32, c3: u32, k0: u32, k1: u32, out4: *mut u32);
+    pub fn rrt_philox_kat_rounds(rounds: c_int, c0: u32, c1: u32, c2: u32, c3: u32, k0: u32, k1: u32, out4: *mut u32) -> c_int;
+    pub fn rrt_philox_rounds() -> c_int;
+    pub fn rrt_kat_light(ctx: *mut RrtCtx, scene: *const RrtScene, n: c_int, origin: *const f64, dir: *const f64, u: *const f64,
+                         pdf_each: *mut f64, pdf_list: *mut f64, random_dir: *mut f64) -> c_int;
+    pub fn rrt_kat_rng(ctx: *mut RrtCtx, seed: u64, pixel: u32, sample0: u32, bounce: u32, block: u32, n: c_int,
+                       raw4: *mut u32, uniform5: *mut f32) -> c_int;
     pub fn rrt_version() -> *const c_char;
     pub fn rrt_last_error() -> *const c_char;
 }

@@ -180,6 +180,9 @@ typedef struct rrt_scene rrt_scene;
  * Debugging switches read from the environment (results are unchanged up to float summation order):
  *   RRT_KERNEL=full        (rrt_init) always run the general render-kernel instance
  *   RRT_NO_STEAL=1         (rrt_init) lanes never take over a neighbour pixel's samples
+ *   RRT_DETERMINISTIC=1    (rrt_init) no stealing and one work item per tile: every pixel is one lane's
+ *                          sum in sample order, one float4 store — frames repeat bit for bit (the default
+ *                          schedule adds per-chunk sums with float atomics in whatever order they finish)
  *   RRT_NO_BOX_LEAVES=1    (rrt_scene_create) axis-aligned boxes stay six separate quad leaves
  *   RRT_NO_FRONT=1         (rrt_scene_create) outsized primitives (a ground sphere) stay in the BVH instead of
  *                          being tested ahead of the traversal */
@@ -250,6 +253,23 @@ int rrt_flatten_check(const rrt_scene_desc* desc, int32_t* n_prims, int32_t* n_n
 int rrt_scene_features(const rrt_scene_desc* desc, int32_t* features);
 void rrt_philox_kat(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1,
                     uint32_t* out4);
+/*   rrt_philox_kat_rounds: the same block at 7 or 10 rounds (Random123 publishes known answers for both);
+ *   rrt_philox_rounds: the round count the render kernel was compiled with (7). */
+int rrt_philox_kat_rounds(int rounds, uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+                          uint32_t k1, uint32_t* out4);
+int rrt_philox_rounds(void);
+
+/* Device-side known-answer hooks (tests; need a GPU).  They run the kernels' own code, not a copy:
+ *   rrt_kat_light: for n (origin, direction) pairs, HittableObject::pdf_value of every entry of the
+ *     scene's light list (quad.rs:93-102, sphere.rs:102-115) -> pdf_each[n * n_lights], the list's mean
+ *     (hittable_list.rs:60-69) -> pdf_list[n], and HittableObject::random(origin) drawn with the two
+ *     uniforms u[2i], u[2i+1] (quad.rs:104-107, sphere.rs:117-122) -> random_dir[n * n_lights * 3].
+ *   rrt_kat_rng: the sampling RNG's blocks for (seed; pixel, sample0 + i, bounce, block), i < n:
+ *     raw4[4n] Philox words and/or uniform5[5n] = the five uniforms (x, y, z, w, v) the kernel draws. */
+int rrt_kat_light(rrt_ctx* ctx, const rrt_scene* scene, int n, const double* origin, const double* dir,
+                  const double* u, double* pdf_each, double* pdf_list, double* random_dir);
+int rrt_kat_rng(rrt_ctx* ctx, uint64_t seed, uint32_t pixel, uint32_t sample0, uint32_t bounce,
+                uint32_t block, int n, uint32_t* raw4, float* uniform5);
 const char* rrt_last_error(void);
 const char* rrt_version(void);
 

@@ -350,8 +350,10 @@ int orc_probe(orc_scene* s, const rrt_camera* cam, int32_t* prim_id, double* t) 
 
 // Camera::render over rows [row_begin, row_end) step row_step.  rgb: W*H*3 doubles of
 // pixel_samples_scale * sum (what write_color receives); rows not rendered are left untouched.
-int orc_render(orc_scene* s, const rrt_camera* cam, int integrator, uint64_t seed, int nthreads, int row_begin,
-               int row_end, int row_step, double* rgb, orc_counters* counters) {
+// rgb_sq (optional): per-pixel mean of the squared per-sample radiance, per channel — the second
+// moment the golden fixtures store so that a test can form standard errors (not a reference output).
+int orc_render_moments(orc_scene* s, const rrt_camera* cam, int integrator, uint64_t seed, int nthreads, int row_begin,
+                       int row_end, int row_step, double* rgb, double* rgb_sq, orc_counters* counters) {
   if (integrator == RRT_INT_BOOK3 && !s->S.lights) { g_err = "book-3 integrator needs a lights list"; return -1; }
   CameraData d; initialize(cam, integrator, d);
   if (row_end > d.image_height) row_end = d.image_height;
@@ -369,25 +371,34 @@ int orc_render(orc_scene* s, const rrt_camera* cam, int integrator, uint64_t see
       int j = rows[k];
       Ctx c(row_seed(seed, j));
       for (int i = 0; i < cam->image_width; ++i) {
-        Color pixel_color(0, 0, 0);
+        Color pixel_color(0, 0, 0), pixel_sq(0, 0, 0);
         if (integrator == RRT_INT_BOOK3) {
           for (int s_j = 0; s_j < d.sqrt_spp; ++s_j)
             for (int s_i = 0; s_i < d.sqrt_spp; ++s_i) {
               Ray r = get_ray(d, i, j, s_i, s_j, c);
               c.n.paths += 1;
-              pixel_color = pixel_color + ray_color_b3(d, S, r, cam->max_depth, c);
+              Color L = ray_color_b3(d, S, r, cam->max_depth, c);
+              pixel_color = pixel_color + L;
+              if (rgb_sq) pixel_sq = pixel_sq + L * L;
             }
         } else {
           for (int sample = 0; sample < cam->samples_per_pixel; ++sample) {
             Ray r = get_ray(d, i, j, 0, 0, c);
             c.n.paths += 1;
-            pixel_color = pixel_color + (integrator == RRT_INT_BOOK1 ? ray_color_b1(d, S, r, cam->max_depth, c)
-                                                                      : ray_color_b2(d, S, r, cam->max_depth, c));
+            Color L = integrator == RRT_INT_BOOK1 ? ray_color_b1(d, S, r, cam->max_depth, c)
+                                                  : ray_color_b2(d, S, r, cam->max_depth, c);
+            pixel_color = pixel_color + L;
+            if (rgb_sq) pixel_sq = pixel_sq + L * L;
           }
         }
         Color out = d.pixel_samples_scale * pixel_color;
         double* px = rgb + ((size_t)j * cam->image_width + i) * 3;
         px[0] = out.x(); px[1] = out.y(); px[2] = out.z();
+        if (rgb_sq) {
+          Color sq = d.pixel_samples_scale * pixel_sq;
+          double* qx = rgb_sq + ((size_t)j * cam->image_width + i) * 3;
+          qx[0] = sq.x(); qx[1] = sq.y(); qx[2] = sq.z();
+        }
       }
       per[tid].add(c.n);
     }
@@ -408,6 +419,11 @@ int orc_render(orc_scene* s, const rrt_camera* cam, int integrator, uint64_t see
     counters->rng_draws = tot.rng_draws;
   }
   return 0;
+}
+
+int orc_render(orc_scene* s, const rrt_camera* cam, int integrator, uint64_t seed, int nthreads, int row_begin,
+               int row_end, int row_step, double* rgb, orc_counters* counters) {
+  return orc_render_moments(s, cam, integrator, seed, nthreads, row_begin, row_end, row_step, rgb, nullptr, counters);
 }
 
 // color.rs:14-42 (book 3 scrubs NaN, books 1-2 do not)

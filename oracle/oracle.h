@@ -29,6 +29,10 @@ void orc_camera_internals(const rrt_camera* cam, int integrator, double* out22);
 int orc_probe(orc_scene* s, const rrt_camera* cam, int32_t* prim_id, double* t);
 int orc_render(orc_scene* s, const rrt_camera* cam, int integrator, uint64_t seed, int nthreads,
                int row_begin, int row_end, int row_step, double* rgb, orc_counters* counters);
+/* as orc_render, plus (rgb_sq, may be NULL) the per-pixel mean of squared per-sample radiance */
+int orc_render_moments(orc_scene* s, const rrt_camera* cam, int integrator, uint64_t seed, int nthreads,
+                       int row_begin, int row_end, int row_step, double* rgb, double* rgb_sq,
+                       orc_counters* counters);
 void orc_write_color(const double* rgb, int n_pixels, int nan_scrub, uint8_t* out);
 void orc_resolve_accum(const float* accum, int n_pixels, uint32_t spp, uint8_t* out);
 int orc_kat_hit(orc_scene* s, const double* origin, const double* dir, double time, double tmin,

@@ -500,6 +500,7 @@ struct Scene {
   std::vector<Material> materials;
   std::vector<Texture> textures;
   std::vector<Perlin> perlins;
+  std::vector<std::vector<uint8_t>> image_store;  // RtwImage owns its pixels (rtw_image.rs:4-8): copied, not borrowed
   HittableRef world, lights;
   bool probe_mode = false;
   std::string error;
@@ -567,6 +568,10 @@ struct Scene {
         perlins[i].perm_z[k] = d->perlins[i].perm_z[k];
       }
     }
+    image_store.resize(d->n_images > 0 ? d->n_images : 0);
+    for (int i = 0; i < d->n_images; ++i)
+      if (d->images[i].rgb && d->images[i].width > 0 && d->images[i].height > 0)
+        image_store[i].assign(d->images[i].rgb, d->images[i].rgb + (size_t)d->images[i].width * d->images[i].height * 3);
     for (int i = 0; i < d->n_textures; ++i) {
       const rrt_texture& t = d->textures[i];
       Texture x;
@@ -574,7 +579,7 @@ struct Scene {
       x.scale = t.scale; x.inv_scale = 1.0 / t.scale;  // texture.rs:51
       x.even = t.even; x.odd = t.odd;
       if (t.kind == RRT_T_IMAGE && t.image >= 0 && t.image < d->n_images && d->images[t.image].rgb) {
-        x.img_w = d->images[t.image].width; x.img_h = d->images[t.image].height; x.img = d->images[t.image].rgb;
+        x.img_w = d->images[t.image].width; x.img_h = d->images[t.image].height; x.img = image_store[t.image].data();
       }
       if (t.kind == RRT_T_NOISE) x.perlin = &perlins[t.perlin];
       textures.push_back(x);

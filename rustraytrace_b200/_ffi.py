@@ -111,6 +111,10 @@ RRT_SYMBOLS = [
     ("rrt_flatten_check", c_int, [C.POINTER(SceneDesc)] + [C.POINTER(c_int)] * 5),
     ("rrt_scene_features", c_int, [C.POINTER(SceneDesc), C.POINTER(c_int)]),
     ("rrt_philox_kat", None, [C.c_uint32] * 6 + [C.POINTER(C.c_uint32)]),
+    ("rrt_philox_kat_rounds", c_int, [c_int] + [C.c_uint32] * 6 + [C.POINTER(C.c_uint32)]),
+    ("rrt_philox_rounds", c_int, []),
+    ("rrt_kat_light", c_int, [VP, VP, c_int, VP, VP, VP, VP, VP, VP]),
+    ("rrt_kat_rng", c_int, [VP, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, c_int, VP, VP]),
     ("rrt_last_error", C.c_char_p, []),
     ("rrt_version", C.c_char_p, []),
 ]

@@ -266,7 +266,9 @@ class Context:
     def scene(self, desc):
         h = C.c_void_p()
         _check(F.rrt().rrt_scene_create(self._h, C.byref(desc), C.byref(h)))
-        return GpuScene(self, h)
+        g = GpuScene(self, h)
+        g.n_lights = self.stats()["n_lights"]
+        return g
 
     @staticmethod
     def params(integrator, seed=1, shard_mode=F.SHARD_NONE, rank=0, world=1):
@@ -311,6 +313,29 @@ class Context:
 
     def resolve_device(self, accum_ptr, width, height, spp, rgb_ptr):
         _check(F.rrt().rrt_resolve_rgb8_device(self._h, accum_ptr, width, height, int(spp), rgb_ptr))
+
+    def kat_light(self, gscene, origin, direction, u):
+        """rrt_kat_light: the device light-sampling code on n queries.  origin, direction (n, 3), u (n, 2).
+        Returns (pdf_each (n, n_lights), pdf_list (n,), random_dir (n, n_lights, 3))."""
+        o = np.ascontiguousarray(origin, dtype=np.float64).reshape(-1, 3)
+        d = np.ascontiguousarray(direction, dtype=np.float64).reshape(-1, 3)
+        uu = np.ascontiguousarray(u, dtype=np.float64).reshape(-1, 2)
+        n = o.shape[0]
+        nl = self.stats()["n_lights"] if gscene is None else gscene.n_lights
+        each = np.zeros((n, nl), dtype=np.float64)
+        lst = np.zeros(n, dtype=np.float64)
+        rnd = np.zeros((n, nl, 3), dtype=np.float64)
+        _check(F.rrt().rrt_kat_light(self._h, gscene._handle, n, o.ctypes.data, d.ctypes.data, uu.ctypes.data,
+                                     each.ctypes.data, lst.ctypes.data, rnd.ctypes.data))
+        return each, lst, rnd
+
+    def kat_rng(self, seed, pixel, sample0, bounce, block, n):
+        """rrt_kat_rng: (raw (n, 4) uint32 Philox words, uniforms (n, 5) float32) of the device RNG."""
+        raw = np.zeros((n, 4), dtype=np.uint32)
+        u5 = np.zeros((n, 5), dtype=np.float32)
+        _check(F.rrt().rrt_kat_rng(self._h, int(seed), int(pixel), int(sample0), int(bounce), int(block), int(n),
+                                   raw.ctypes.data, u5.ctypes.data))
+        return raw, u5
 
     def stats(self):
         s = F.Stats()

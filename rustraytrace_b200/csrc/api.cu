@@ -41,6 +41,7 @@ struct rrt_ctx {
   size_t accum_floats = 0;
   rrt_stats stats;
   bool no_steal = false;              // RRT_NO_STEAL=1: lanes never take over neighbours' samples (debugging / A-B)
+  bool deterministic = false;         // RRT_DETERMINISTIC=1: no stealing, one chunk per tile -> bit-reproducible frames
   bool force_full_kernel = false;     // RRT_KERNEL=full: always run the SF_ALL render kernel instance (include/rrt.h)
   std::vector<rrt_scene*> scenes;  // live scenes of this context (released by rrt_shutdown if the caller did not)
 };
@@ -98,6 +99,7 @@ int rrt_init(int device, rrt_ctx** out) {
   const char* kv = std::getenv("RRT_KERNEL");
   c->force_full_kernel = kv && std::strcmp(kv, "full") == 0;
   c->no_steal = std::getenv("RRT_NO_STEAL") != nullptr;
+  c->deterministic = std::getenv("RRT_DETERMINISTIC") != nullptr;
   CK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking), "cudaStreamCreate");
   c->stream = c->own_stream;
   for (auto& ev : c->ev) CK(cudaEventCreate(&ev), "cudaEventCreate");
@@ -157,6 +159,8 @@ int rrt_scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out) {
   std::string err;
   int st = flatten_scene(desc, F, err);
   if (st != RRT_OK) return fail(st, "scene flatten failed: " + err);
+  if (F.bvh_depth >= RRT_STACK)   // the traversal stack holds one entry per level (intersect.cuh)
+    return fail(RRT_ERR_UNSUPPORTED, "BVH depth " + std::to_string(F.bvh_depth) + " exceeds the traversal stack (" + std::to_string(RRT_STACK) + ")");
   CK(cudaSetDevice(c->device), "cudaSetDevice");
   rrt_scene* sc = new rrt_scene();
   sc->ctx = c;
@@ -166,7 +170,7 @@ int rrt_scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out) {
   int rc = RRT_OK;
   if ((rc = upload(sc, F.prims, &D.prims)) || (rc = upload(sc, F.prims64, &D.prims64)) ||
       (rc = upload(sc, F.nodes, &D.nodes)) || (rc = upload(sc, F.bprims, &D.bprims)) ||
-      (rc = upload(sc, F.boxes, &D.boxes)) ||
+      (rc = upload(sc, F.boxes, &D.boxes)) || (rc = upload(sc, F.qpairs, &D.qpairs)) ||
       (rc = upload(sc, F.materials, &D.materials)) || (rc = upload(sc, F.textures, &D.textures)) ||
       (rc = upload(sc, F.images, &D.images)) || (rc = upload(sc, F.texels, &texels)) ||
       (rc = upload(sc, F.perlins, &D.perlins)) || (rc = upload(sc, F.media, &D.media)) ||
@@ -205,6 +209,10 @@ static int check_camera(const rrt_camera* cam, const rrt_render_params* p) {
   if (!cam) return fail(RRT_ERR_INVALID, "camera is null");
   if (cam->image_width < 1 || cam->image_width > 65536 || !(cam->aspect_ratio > 0.0))
     return fail(RRT_ERR_INVALID, "camera: image_width/aspect_ratio out of range");
+  // pixel indices are 32-bit in the kernels (rng.pixel, py * width + px): cap the frame at 2^30 pixels
+  // (a 16 GiB RGBA-sum frame) instead of overflowing
+  if ((double)cam->image_width / cam->aspect_ratio * (double)cam->image_width > 1073741824.0)
+    return fail(RRT_ERR_INVALID, "camera: frame larger than 2^30 pixels");
   if (p) {
     if (p->integrator < RRT_INT_BOOK1 || p->integrator > RRT_INT_BOOK3) return fail(RRT_ERR_INVALID, "params: unknown integrator");
     if (p->shard_mode < RRT_SHARD_NONE || p->shard_mode > RRT_SHARD_SAMPLE) return fail(RRT_ERR_INVALID, "params: unknown shard mode");
@@ -269,7 +277,7 @@ int rrt_render_device(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, co
   // Sample stealing (render_kernel.cuh) pays wherever path cost varies inside a warp (C1 +20 %, C2/C3a
   // +3.5 %, C5 +1-6 %).  Not for one- and two-primitive scenes (near-constant path cost; the shared
   // counters cost 9 % on C3b) nor for the Perlin instances, which sit at their register limit (C4 -4 %).
-  const bool steal = sc->n_prims > 2 && !(variant->features & SF_NOISE) && !c->no_steal;
+  const bool steal = sc->n_prims > 2 && !(variant->features & SF_NOISE) && !c->no_steal && !c->deterministic;
   int bps = render_blocks_per_sm(variant, steal);
   if (bps < 1) return fail(RRT_ERR_CUDA, "kernel launch failed: render kernel does not fit on an SM");
   const int grid = c->sm_count * bps;
@@ -281,6 +289,7 @@ int rrt_render_device(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, co
     long long want = ((steal ? 96 : 48) * resident_warps + W.n_tiles - 1) / W.n_tiles;
     long long cap = std::max(1, n_samples / (steal ? 8 : 16));
     chunks = std::max(1LL, std::min(want, cap));
+    if (c->deterministic) chunks = 1;   // one float4 store per pixel, samples summed in index order by one lane
   }
   W.chunks = (int)chunks;
   W.atomic_accum = chunks > 1 ? 1 : 0;
@@ -439,6 +448,72 @@ int rrt_get_stats(const rrt_ctx* c, rrt_stats* out) {
 // Known-answer hook for the sampling RNG (tests): Philox4x32-10 block.
 void rrt_philox_kat(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t* out4) {
   philox4x32_10(c0, c1, c2, c3, k0, k1, out4);
+}
+
+// The same block at any round count Random123 publishes known answers for (7 and 10); 0 = unsupported.
+int rrt_philox_kat_rounds(int rounds, uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t* out4) {
+  if (!out4) return fail(RRT_ERR_INVALID, "rrt_philox_kat_rounds: out4 is null");
+  if (rounds == 7) philox4x32<7>(c0, c1, c2, c3, k0, k1, out4);
+  else if (rounds == 10) philox4x32<10>(c0, c1, c2, c3, k0, k1, out4);
+  else return fail(RRT_ERR_INVALID, "rrt_philox_kat_rounds: rounds must be 7 or 10");
+  return RRT_OK;
+}
+int rrt_philox_rounds(void) { return RRT_PHILOX_ROUNDS; }
+
+// Device-side known-answer hooks (tests): run the kernels' own light-sampling and RNG code.
+int rrt_kat_light(rrt_ctx* c, const rrt_scene* sc, int n, const double* origin, const double* dir, const double* u,
+                  double* pdf_each, double* pdf_list, double* random_dir) {
+  if (!c || !sc || n < 0 || !origin || !dir || !u || !pdf_each || !pdf_list || !random_dir)
+    return fail(RRT_ERR_INVALID, "rrt_kat_light: null argument");
+  if (sc->ctx != c) return fail(RRT_ERR_INVALID, "scene belongs to another (or a shut down) context");
+  if (n == 0) return RRT_OK;
+  CK(cudaSetDevice(c->device), "cudaSetDevice");
+  const int nl = sc->n_lights;
+  const size_t n_in = (size_t)n * 8, n_out = (size_t)n * ((size_t)nl * 4 + 1);
+  std::vector<float> hin(n_in), hout(n_out);
+  for (int i = 0; i < n; ++i) {
+    for (int k = 0; k < 3; ++k) { hin[3 * (size_t)i + k] = (float)origin[3 * (size_t)i + k]; hin[3 * (size_t)n + 3 * (size_t)i + k] = (float)dir[3 * (size_t)i + k]; }
+    hin[6 * (size_t)n + 2 * (size_t)i] = (float)u[2 * (size_t)i]; hin[6 * (size_t)n + 2 * (size_t)i + 1] = (float)u[2 * (size_t)i + 1];
+  }
+  float* din = nullptr; float* dout = nullptr;
+  CK(cudaMalloc(&din, n_in * sizeof(float)), "cudaMalloc(kat)");
+  cudaError_t e = cudaMalloc(&dout, std::max<size_t>(1, n_out) * sizeof(float));
+  if (e == cudaSuccess) e = cudaMemcpyAsync(din, hin.data(), n_in * sizeof(float), cudaMemcpyHostToDevice, c->stream);
+  KatLightArgs A;
+  std::memset(&A, 0, sizeof A);
+  A.S = sc->dev; A.n = n;
+  A.origin = din; A.dir = din + 3 * (size_t)n; A.u = din + 6 * (size_t)n;
+  A.pdf_each = dout; A.pdf_list = dout + (size_t)n * nl; A.random_dir = dout + (size_t)n * nl + n;
+  if (e == cudaSuccess) e = launch_kat_light(A, c->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(hout.data(), dout, n_out * sizeof(float), cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+  cudaFree(din); if (dout) cudaFree(dout);
+  if (e != cudaSuccess) return fail(RRT_ERR_CUDA, std::string("kat kernel failed: ") + cudaGetErrorString(e));
+  for (size_t i = 0; i < (size_t)n * nl; ++i) pdf_each[i] = hout[i];
+  for (size_t i = 0; i < (size_t)n; ++i) pdf_list[i] = hout[(size_t)n * nl + i];
+  for (size_t i = 0; i < (size_t)n * nl * 3; ++i) random_dir[i] = hout[(size_t)n * nl + n + i];
+  c->stats.kernel_launches = 1;
+  return RRT_OK;
+}
+
+int rrt_kat_rng(rrt_ctx* c, uint64_t seed, uint32_t pixel, uint32_t sample0, uint32_t bounce, uint32_t block, int n,
+                uint32_t* raw4, float* uniform5) {
+  if (!c || n < 0 || (!raw4 && !uniform5)) return fail(RRT_ERR_INVALID, "rrt_kat_rng: bad argument");
+  if (n == 0) return RRT_OK;
+  CK(cudaSetDevice(c->device), "cudaSetDevice");
+  uint32_t* draw = nullptr; float* du = nullptr;
+  cudaError_t e = cudaSuccess;
+  if (raw4) e = cudaMalloc(&draw, (size_t)n * 16);
+  if (e == cudaSuccess && uniform5) e = cudaMalloc(&du, (size_t)n * 20);
+  if (e == cudaSuccess) e = launch_kat_rng((unsigned)(seed & 0xffffffffu), (unsigned)(seed >> 32), pixel, sample0, bounce, block, n, draw, du, c->stream);
+  if (e == cudaSuccess && raw4) e = cudaMemcpyAsync(raw4, draw, (size_t)n * 16, cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess && uniform5) e = cudaMemcpyAsync(uniform5, du, (size_t)n * 20, cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+  if (draw) cudaFree(draw);
+  if (du) cudaFree(du);
+  if (e != cudaSuccess) return fail(RRT_ERR_CUDA, std::string("kat kernel failed: ") + cudaGetErrorString(e));
+  c->stats.kernel_launches = 1;
+  return RRT_OK;
 }
 
 }  // extern "C"

@@ -29,6 +29,14 @@ namespace rrt {
 // f64 twin (double q[16]):
 // sphere: q0..2 = c0, q3 = r, q4..6 = dc
 // quad:   q0..2 = n, q3 = d, q4..6 = Q, q7..9 = u, q10..12 = v, q13..15 = w   (quad.rs formulas verbatim)
+// quad pair record (float4 q[6]), only for the quads of a brute-force root leaf (scenes of <= 16
+// primitives: the Cornell boxes): two quads side by side in every 64-bit pair, so that the plane,
+// alpha and beta equations of both are packed FMAs (fma.rn.f32x2) and the whole leaf is straight-line
+// code with predicated accepts instead of three divergent early-outs per quad.
+//   q0 = (n0.x, n1.x, n0.y, n1.y)  q1 = (n0.z, n1.z, d0, d1)
+//   q2 = (A0.x, A1.x, A0.y, A1.y)  q3 = (A0.z, A1.z, a0_0, a0_1)
+//   q4 = (B0.x, B1.x, B0.y, B1.y)  q5 = (B0.z, B1.z, b0_0, b0_1)
+// Pair k holds quads first+2k and first+2k+1 of the leaf's quad run; a missing partner has n = 0.
 enum PrimKind { PRIM_SPHERE = 0, PRIM_QUAD = 1 };
 enum PrimFlags { PF_UV_ROTATED = 1 };
 
@@ -44,6 +52,10 @@ enum PrimFlags { PF_UV_ROTATED = 1 };
 // boxes[2*box] = (lo.xyz, first as int bits), boxes[2*box+1] = (hi.xyz, 0); the quads sit at
 // first .. first+5 in face order -x, +x, -y, +y, -z, +z.  The f32 kernel slab-tests the box, runs the
 // real quad test on the entry face only, and falls back to all six whenever that is not conclusive.
+// Traversal stack entries per lane (intersect.cuh).  The flattener switches to median splits at depth 40
+// (flatten.cpp), so a tree over fewer than 2^24 primitives is shallower than this; rrt_scene_create
+// refuses a deeper one (RRT_ERR_UNSUPPORTED) instead of letting the kernel drop a subtree.
+#define RRT_STACK 64
 static const int LEAF_BOX_MARK = 0xFF;
 static const int LEAF_MAX_PER_KIND = 15;
 inline
@@ -142,6 +154,7 @@ struct DevScene {
   const float4* nodes;
   const float4* bprims;
   const float4* boxes;   // two float4 per box leaf
+  const float4* qpairs;  // quad pair records of a brute-force root leaf, or null
   const double* prims64;
   const DevMaterial* materials;
   const DevTexture* textures;

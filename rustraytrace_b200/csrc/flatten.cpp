@@ -837,7 +837,27 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
       emitted += n.count;
     }
   }
-  if (B.nodes[root].left < 0) { out.root_ref = leaf_ref[root]; return RRT_OK; }
+  if (B.nodes[root].left < 0) {
+    out.root_ref = leaf_ref[root];
+    // Brute-force root leaf: its quads again as pair records for the packed plane tests of
+    // quad_pairs_hit32 (device_types.h); an odd count is padded with a quad of normal 0, which the
+    // |denom| >= 1e-8 test of quad.rs:67 rejects.
+    const int leaf = ~out.root_ref, first = leaf >> 8, ns = (leaf >> 4) & 15, nq = leaf & 15;
+    if ((leaf & 0xFF) != LEAF_BOX_MARK && nq > 0 && !std::getenv("RRT_NO_QUAD_PAIRS")) {
+      for (int k = 0; k < nq; k += 2) {
+        float4 a[3], b[3];
+        for (int j = 0; j < 3; ++j) {
+          a[j] = out.prims[4 * (first + ns + k) + j];
+          b[j] = k + 1 < nq ? out.prims[4 * (first + ns + k + 1) + j] : f4(0, 0, 0, 0);
+        }
+        for (int j = 0; j < 3; ++j) {   // (x0, x1, y0, y1) / (z0, z1, w0, w1) of plane, alpha and beta rows
+          out.qpairs.push_back(f4(a[j].x, b[j].x, a[j].y, b[j].y));
+          out.qpairs.push_back(f4(a[j].z, b[j].z, a[j].w, b[j].w));
+        }
+      }
+    }
+    return RRT_OK;
+  }
   // inner nodes breadth-first
   std::vector<int> inner_index(B.nodes.size(), -1);
   std::vector<int> bfs;

@@ -20,7 +20,6 @@
 
 namespace rrt {
 
-#define RRT_STACK 64
 #define PRIM_QUAD_BIT 0x40000000
 
 struct Ray32 {
@@ -194,6 +193,59 @@ __device__ __forceinline__ void slab2(float4 n0, float4 n1, float4 n2, float idx
   far1 = fminf(fminf(fx.y, fy.y), fminf(fz.y, tmax));
 }
 
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) {
+  unsigned long long ra, rb, rd;
+  ra = *reinterpret_cast<unsigned long long*>(&a);
+  rb = *reinterpret_cast<unsigned long long*>(&b);
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(rd) : "l"(ra), "l"(rb));
+  return *reinterpret_cast<float2*>(&rd);
+}
+
+// The quads of a brute-force root leaf, two at a time (device_types.h quad pair record): Quad::hit
+// (quad.rs:64-91) for both as 16 packed FMAs and two reciprocals, every lane running the same
+// straight-line code; the reference's early-outs (parallel, t out of range, alpha / beta outside
+// [0, 1]) become one predicate per quad.  Quads are accepted in leaf order with t <= h.t, like the loop
+// of quad_hit32 calls this replaces, so the equal-t rules are unchanged.
+__device__ __forceinline__ void quad_pairs_hit32(const float4* __restrict__ prims, const float4* __restrict__ qp, int first, int nq,
+                                                 const Ray32& r, float tmin, int skip, Hit32& h) {
+  const float2 ox = bcast2(r.o.x), oy = bcast2(r.o.y), oz = bcast2(r.o.z);
+  const float2 dx = bcast2(r.d.x), dy = bcast2(r.d.y), dz = bcast2(r.d.z);
+  for (int k = 0; k < nq; k += 2) {
+    const float4* g = qp + 3 * k;
+    const float4 q0 = ldg4(g), q1 = ldg4(g + 1), q2 = ldg4(g + 2), q3 = ldg4(g + 3), q4 = ldg4(g + 4), q5 = ldg4(g + 5);
+    const float2 nx = make_float2(q0.x, q0.y), ny = make_float2(q0.z, q0.w), nz = make_float2(q1.x, q1.y);
+    const float2 denom = fma2(nz, dz, fma2(ny, dy, mul2(nx, dx)));
+    const float2 num = fma2(neg2(nz), oz, fma2(neg2(ny), oy, fma2(neg2(nx), ox, make_float2(q1.z, q1.w))));  // d - n.o
+    const float2 t = make_float2(num.x / denom.x, num.y / denom.y);
+    const float2 px = fma2(t, dx, ox), py = fma2(t, dy, oy), pz = fma2(t, dz, oz);
+    const float2 al = fma2(pz, make_float2(q3.x, q3.y), fma2(py, make_float2(q2.z, q2.w), fma2(px, make_float2(q2.x, q2.y), make_float2(q3.z, q3.w))));
+    const float2 be = fma2(pz, make_float2(q5.x, q5.y), fma2(py, make_float2(q4.z, q4.w), fma2(px, make_float2(q4.x, q4.y), make_float2(q5.z, q5.w))));
+    const int i0 = first + k, i1 = first + k + 1;
+    bool ok0 = (fabsf(denom.x) >= 1e-8f) & (t.x >= tmin) & (t.x <= h.t) & (al.x >= 0.0f) & (al.x <= 1.0f) & (be.x >= 0.0f) & (be.x <= 1.0f) & (i0 != skip);
+    if (ok0 && t.x == h.t) ok0 = tie_accept(prims, i0 | PRIM_QUAD_BIT, h.prim);
+    if (ok0) { h.t = t.x; h.prim = i0 | PRIM_QUAD_BIT; }
+    bool ok1 = (fabsf(denom.y) >= 1e-8f) & (t.y >= tmin) & (t.y <= h.t) & (al.y >= 0.0f) & (al.y <= 1.0f) & (be.y >= 0.0f) & (be.y <= 1.0f) & (i1 != skip);
+    if (ok1 && t.y == h.t) ok1 = tie_accept(prims, i1 | PRIM_QUAD_BIT, h.prim);
+    if (ok1) { h.t = t.y; h.prim = i1 | PRIM_QUAD_BIT; }
+  }
+}
+
+// The brute-force root leaf (scenes of at most RRT_SINGLE_LEAF_MAX primitives): spheres one by one,
+// quads as pairs when the flattener supplied pair records.
+template <int FEAT>
+__device__ __forceinline__ void root_leaf_hit32(const DevScene& S, int leaf, const Ray32& r, float a, float inv_a, float tmin,
+                                                int skip, bool motion, Hit32& h) {
+  int first = leaf >> 8, ns = (leaf >> 4) & 15, nq = leaf & 15;
+  for (int k = 0; k < ns; ++k) sphere_hit32(S.prims, first + k, r, a, inv_a, tmin, skip, motion, h);
+  first += ns;
+  if (FEAT & SF_QUADS) {
+    // not in the instances with box leaves (the book-2 final scene): a scene with box leaves has a tree, and
+    // those instances sit at their register limit
+    if (!(FEAT & SF_BOXES) && S.qpairs) quad_pairs_hit32(S.prims, S.qpairs, first, nq, r, tmin, skip, h);
+    else for (int k = 0; k < nq; ++k) quad_hit32(S.prims, first + k, r, tmin, skip, h);
+  }
+}
+
 // A leaf below the root holds exactly one primitive (or one box): the flattener builds the tree down
 // to single primitives (flatten.hpp max_leaf = 1), so the traversal loop needs no per-leaf loops.
 template <int FEAT>
@@ -212,8 +264,8 @@ __device__ inline void world_hit32(const DevScene& S, const Ray32& r, float tmin
   const float inv_a = 1.0f / a;
   const bool motion = (FEAT & SF_MOTION) && S.has_motion != 0;
   int cur = S.root_ref;
-  if (cur < 0) {  // the whole scene is one leaf: brute force, uniform control flow
-    leaf_hit32<FEAT>(S.prims, S.boxes, ~cur, r, V3f(0.0f, 0.0f, 0.0f), a, inv_a, tmin, skip, motion, h);  // a root leaf is never a box leaf
+  if (cur < 0) {  // the whole scene is one leaf: brute force, uniform control flow (a root leaf is never a box leaf)
+    root_leaf_hit32<FEAT>(S, ~cur, r, a, inv_a, tmin, skip, motion, h);
     return;
   }
   // front run (flatten.cpp): primitives spanning most of the scene, tested by all lanes together
@@ -273,6 +325,25 @@ __device__ inline void world_hit32(const DevScene& S, const Ray32& r, float tmin
     }
   }
 }
+// Both boundary hits of ConstantMedium::hit (constant_medium.rs:41-42) when the boundary is one sphere:
+// boundary.hit(r, UNIVERSE) returns the smaller root whatever its sign (sphere.rs:81-89), and the second
+// call on (t1 + 0.0001, inf) can then only return the larger one — one discriminant instead of two.
+__device__ inline bool boundary_sphere_span32(const float4* __restrict__ bprims, const DevMedium& m, const Ray32& r,
+                                              float a, float inv_a, bool motion, float& t1, float& t2) {
+  const float4 p0 = ldg4(bprims + 4 * m.first);
+  V3f c(p0.x, p0.y, p0.z);
+  if (motion) { float4 p1 = ldg4(bprims + 4 * m.first + 1); c = c + r.tm * V3f(p1.x, p1.y, p1.z); }
+  const V3f oc = c - r.o;
+  const float hh = dot(r.d, oc);
+  const V3f perp = oc - (hh * inv_a) * r.d;
+  const float disc = p0.w * p0.w - dot(perp, perp);
+  if (disc < 0.0f) return false;
+  const float sq = sqrtf(disc * a);
+  t1 = (hh - sq) * inv_a;
+  t2 = (hh + sq) * inv_a;
+  return t2 > t1 + 0.0001f;
+}
+
 // Closest hit of a medium boundary run in [lo, hi] for quads / (lo, hi) for spheres
 // (boundary.hit(r, interval), constant_medium.rs:41-42).  Returns t or -1 flagged by `found`.
 __device__ inline bool boundary_hit32(const float4* __restrict__ bprims, const DevMedium& m, const Ray32& r,

@@ -10,6 +10,8 @@
 #include "device_types.h"
 #include "intersect.cuh"
 #include "kernels.h"
+#include "rng.cuh"
+#include "shade.cuh"
 #include "vecmath.cuh"
 
 namespace rrt {
@@ -54,7 +56,55 @@ __global__ void resolve_kernel(const float4* __restrict__ accum, int n, int spp,
 }
 
 // ------------------------------------------------------------------------------------------------
+// known-answer hooks: the DEVICE code of the book-3 light sampling (shade.cuh light_pdf / light_random,
+// = quad.rs:93-107, sphere.rs:102-122, hittable_list.rs:60-75) and of the sampling RNG (rng.cuh), driven
+// with caller-chosen arguments so that tests can hold them against closed forms and the oracle.
+__global__ void kat_light_kernel(const __grid_constant__ KatLightArgs A) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= A.n) return;
+  const V3f o(A.origin[3 * i], A.origin[3 * i + 1], A.origin[3 * i + 2]);
+  const V3f d(A.dir[3 * i], A.dir[3 * i + 1], A.dir[3 * i + 2]);
+  const int nl = A.S.n_lights;
+  float sum = 0.0f;
+  for (int l = 0; l < nl; ++l) {
+    const float p = light_pdf(A.S.lights[l], o, d);
+    sum += p;
+    A.pdf_each[(size_t)i * nl + l] = p;
+    const V3f r = light_random(A.S.lights[l], o, A.u[2 * i], A.u[2 * i + 1]);
+    float* dst = A.random_dir + ((size_t)i * nl + l) * 3;
+    dst[0] = r.x; dst[1] = r.y; dst[2] = r.z;
+  }
+  A.pdf_list[i] = nl > 0 ? sum / (float)nl : 0.0f;   // hittable_list.rs:60-69
+}
+
+__global__ void kat_rng_kernel(unsigned k0, unsigned k1, unsigned pixel, unsigned sample0, unsigned bounce, unsigned block,
+                               int n, uint32_t* raw4, float* u5) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  PathRng rng;
+  rng.pixel = pixel; rng.sample = sample0 + (unsigned)i; rng.k0 = k0; rng.k1 = k1;
+  if (raw4) philox4x32<RRT_PHILOX_ROUNDS>(rng.pixel, rng.sample, bounce, block, k0, k1, raw4 + 4 * (size_t)i);
+  if (u5) {
+    const Rand4 r = rng.draw(bounce, block);
+    float* dst = u5 + 5 * (size_t)i;
+    dst[0] = r.x; dst[1] = r.y; dst[2] = r.z; dst[3] = r.w; dst[4] = r.v;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // launchers (host)
+cudaError_t launch_kat_light(const KatLightArgs& A, cudaStream_t st) {
+  if (A.n <= 0) return cudaSuccess;
+  kat_light_kernel<<<(A.n + 127) / 128, 128, 0, st>>>(A);
+  return cudaGetLastError();
+}
+cudaError_t launch_kat_rng(unsigned k0, unsigned k1, unsigned pixel, unsigned sample0, unsigned bounce, unsigned block, int n,
+                           uint32_t* raw4, float* u5, cudaStream_t st) {
+  if (n <= 0) return cudaSuccess;
+  kat_rng_kernel<<<(n + 255) / 256, 256, 0, st>>>(k0, k1, pixel, sample0, bounce, block, n, raw4, u5);
+  return cudaGetLastError();
+}
+
 const RenderVariant* select_render_variant(int integrator, int features, bool force_full) {
   int n = 0;
   const RenderVariant* t = integrator == RRT_INT_BOOK1 ? render_variants_book1(&n)

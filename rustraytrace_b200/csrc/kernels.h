@@ -25,6 +25,17 @@ struct ProbeArgs {
   double* t;
 };
 
+struct KatLightArgs {   // rrt_kat_light: n queries against the scene's light list
+  DevScene S;
+  int n;
+  const float* origin;   // n x 3
+  const float* dir;      // n x 3
+  const float* u;        // n x 2 uniforms for random()
+  float* pdf_each;       // n x n_lights
+  float* pdf_list;       // n
+  float* random_dir;     // n x n_lights x 3
+};
+
 // Resident CTAs per SM each render kernel instance is compiled for (its register budget).  Every
 // instance without Perlin noise fits 64 registers spill-free: 8 CTAs, 32 warps per SM.  The
 // turbulence loop (7 octaves of 8 gradient lookups) pushes an instance to 80 registers (6 CTAs).
@@ -61,6 +72,9 @@ cudaError_t launch_render(const RenderVariant* v, bool steal, const RenderArgs& 
 int render_blocks_per_sm(const RenderVariant* v, bool steal);
 cudaError_t launch_probe(const ProbeArgs& A, int precision, cudaStream_t st);
 cudaError_t launch_probe64(const ProbeArgs& A, cudaStream_t st);  // probe64.cu (-fmad=false)
+cudaError_t launch_kat_light(const KatLightArgs& A, cudaStream_t st);
+cudaError_t launch_kat_rng(unsigned k0, unsigned k1, unsigned pixel, unsigned sample0, unsigned bounce, unsigned block, int n,
+                           uint32_t* raw4, float* u5, cudaStream_t st);
 cudaError_t launch_resolve(const float* accum, int n, int spp, unsigned char* rgb, cudaStream_t st);
 
 }  // namespace rrt

@@ -122,8 +122,13 @@ __device__ __forceinline__ bool shade_step(const DevScene& S, const DevCamera& C
     for (int m = 0; m < S.n_media; ++m) {
       const DevMedium M = S.media[m];
       float t1, t2;
-      if (!boundary_hit32(S.bprims, M, ray, a, inv_a, -CUDART_INF_F, CUDART_INF_F, (FEAT & SF_MOTION) && S.has_motion != 0, t1)) continue;
-      if (!boundary_hit32(S.bprims, M, ray, a, inv_a, t1 + 0.0001f, CUDART_INF_F, (FEAT & SF_MOTION) && S.has_motion != 0, t2)) continue;
+      const bool motion = (FEAT & SF_MOTION) && S.has_motion != 0;
+      if (M.nsph == 1 && M.nquad == 0) {   // one sphere (both media of the book-2 final scene): one discriminant
+        if (!boundary_sphere_span32(S.bprims, M, ray, a, inv_a, motion, t1, t2)) continue;
+      } else {
+        if (!boundary_hit32(S.bprims, M, ray, a, inv_a, -CUDART_INF_F, CUDART_INF_F, motion, t1)) continue;
+        if (!boundary_hit32(S.bprims, M, ray, a, inv_a, t1 + 0.0001f, CUDART_INF_F, motion, t2)) continue;
+      }
       if (t1 < 0.001f) t1 = 0.001f;
       if (t2 > h.t) t2 = h.t;
       if (t1 >= t2) continue;
@@ -307,6 +312,14 @@ render_kernel(const __grid_constant__ RenderArgs A) {
     const int s0 = W.s_begin + (int)(((long long)n_samples * chunk) / W.chunks);
     const int s1 = W.s_begin + (int)(((long long)n_samples * (chunk + 1)) / W.chunks);
 
+    if (W.max_depth <= 0) {  // ray_color(r, depth <= 0) is black for every sample (camera.rs:185-187; b1 :183-185)
+      if (valid) {
+        float4* dst = A.accum + (size_t)py * W.width + px;
+        if (W.atomic_accum) atomicAdd(&dst->w, (float)(s1 - s0));
+        else *dst = make_float4(0.0f, 0.0f, 0.0f, (float)(s1 - s0));
+      }
+      continue;
+    }
     PathRng rng;
     rng.pixel = (uint32_t)(py * W.width + px);
     rng.sample = 0;

@@ -157,10 +157,13 @@ bool decode_jpeg(const std::vector<uint8_t>& file, LoadedImage& out, std::string
         h.build();
       }
     } else if (m == 0xC0 || m == 0xC1) {  // SOF0 / SOF1 (extended sequential, Huffman)
+      if (L < 8) { err = "bad SOF"; return false; }
       if (s[0] != 8) { err = "only 8-bit JPEG is supported"; return false; }
       height = rd16(s + 1); width = rd16(s + 3);
       int nc = s[5];
       if ((nc != 1 && nc != 3) || width < 1 || height < 1) { err = "unsupported component count"; return false; }
+      if (L < 8 + 3 * nc) { err = "bad SOF"; return false; }   // the component table must fit its segment
+      if ((long long)width * height > (1LL << 28)) { err = "image too large"; return false; }
       comp.resize(nc);
       for (int k = 0; k < nc; ++k) {
         comp[k].id = s[6 + 3 * k]; comp[k].h = s[7 + 3 * k] >> 4; comp[k].v = s[7 + 3 * k] & 15; comp[k].tq = s[8 + 3 * k] & 3;
@@ -170,14 +173,19 @@ bool decode_jpeg(const std::vector<uint8_t>& file, LoadedImage& out, std::string
     } else if (m == 0xC2 || (m >= 0xC5 && m <= 0xCF && m != 0xC8 && m != 0xCC)) {
       err = "progressive / lossless / arithmetic JPEG is not supported (baseline only)"; return false;
     } else if (m == 0xDD) {
+      if (L < 4) { err = "bad DRI"; return false; }
       restart = rd16(s);
     } else if (m == 0xDA) {  // SOS: one interleaved scan holding every component
       if (comp.empty()) { err = "SOS before SOF"; return false; }
+      if (L < 3) { err = "bad SOS"; return false; }
       int ns = s[0];
       if (ns != (int)comp.size()) { err = "non-interleaved scans are not supported"; return false; }
+      if (L < 6 + 2 * ns) { err = "bad SOS"; return false; }
       for (int k = 0; k < ns; ++k) {
         int cid = s[1 + 2 * k];
-        for (auto& c : comp) if (c.id == cid) { c.td = s[2 + 2 * k] >> 4; c.ta = s[2 + 2 * k] & 15; }
+        const int td = s[2 + 2 * k] >> 4, ta = s[2 + 2 * k] & 15;
+        if (td > 3 || ta > 3) { err = "bad SOS"; return false; }   // dc[4], ac[4]
+        for (auto& c : comp) if (c.id == cid) { c.td = td; c.ta = ta; }
       }
       i += L;
       const int mcux = (width + 8 * hmax - 1) / (8 * hmax), mcuy = (height + 8 * vmax - 1) / (8 * vmax);

@@ -2,11 +2,9 @@
 (pixel-centre rays, no jitter/defocus, time 0, media excluded) from the ORACLE at width 96, with the
 scene seed 0x5EED1234.  The reference itself cannot be run here (no Rust toolchain, and it has no
 object ids), so these vectors pin the oracle + scene builders against regressions and give the GPU
-tests an oracle-free target.  Also writes tests/golden/radiance_means.json: converged mean linear
-radiance per scene from the oracle (64x? frame, 4096 spp), the target of the mean-radiance gate.
-Run here (CPU):  python scripts/make_golden.py [--radiance]
+tests an oracle-free target.  (Converged images and frame means: scripts/make_golden_converged.py.)
+Run here (CPU):  python scripts/make_golden.py
 """
-import json
 import os
 import sys
 
@@ -33,15 +31,6 @@ def main():
         ids, t = O.OracleScene(s.desc).probe(s.camera)
         np.savez_compressed(os.path.join(GOLD, f"probe_{name(book, no)}.npz"), ids=ids.astype(np.int16 if ids.max() < 32767 else np.int32), t=t)
         print(name(book, no), ids.shape, "hit fraction", float((ids >= 0).mean()))
-    if "--radiance" in sys.argv:
-        out = {}
-        for book, no in SCENES:
-            s = R.BookScene(book, no, overrides=dict(image_width=48, samples_per_pixel=4096, max_depth=50))
-            rgb, _ = O.OracleScene(s.desc).render(s.camera, s.integrator, seed=2024)
-            out[name(book, no)] = dict(mean=[float(x) for x in np.nanmean(rgb, axis=(0, 1))], width=48, spp=4096, depth=50, seed=2024)
-            print(name(book, no), out[name(book, no)]["mean"], flush=True)
-        with open(os.path.join(GOLD, "radiance_means.json"), "w") as f:
-            json.dump(out, f, indent=1, sort_keys=True)
 
 
 if __name__ == "__main__":

@@ -25,7 +25,7 @@ def main():
     tag = sys.argv[1] if len(sys.argv) > 1 else "r01"
     names = sys.argv[2].split(",") if len(sys.argv) > 2 else list(configs.CONFIGS)
     cpu_seconds = float(os.environ.get("CPU_SECONDS", "6"))
-    gold = json.load(open(os.path.join(ROOT, "tests", "golden", "radiance_means.json")))
+    gold = json.load(open(os.path.join(ROOT, "tests", "golden", "converged_manifest.json")))
     threads = os.cpu_count() or 1
     ctx = R.Context(0)
     out = {}
@@ -55,7 +55,7 @@ def main():
         cpu_dt = time.perf_counter() - t0
         mp = st["paths"] / st["kernel_ms"] / 1e3
         fp = configs.F_PATH[key]
-        gm = np.array(gold[GOLD_NAME[key]]["mean"])
+        gm = np.array(gold[GOLD_NAME[key]]["frame_mean"])
         out[key] = dict(
             workload=configs.DESCRIPTION[key], width=s.width, height=s.height, spp=st["spp_effective"], paths=st["paths"],
             kernel_ms=round(st["kernel_ms"], 2), mpaths_s=round(mp, 1), flops_per_path=fp,

@@ -41,6 +41,8 @@ def lib():
         L.orc_probe.argtypes = [VP, C.POINTER(F.Camera), VP, VP]
         L.orc_render.argtypes = [VP, C.POINTER(F.Camera), C.c_int, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int,
                                  VP, C.POINTER(Counters)]
+        L.orc_render_moments.argtypes = [VP, C.POINTER(F.Camera), C.c_int, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int,
+                                         VP, VP, C.POINTER(Counters)]
         L.orc_write_color.argtypes = [VP, C.c_int, C.c_int, VP]
         L.orc_resolve_accum.argtypes = [VP, C.c_int, C.c_uint32, VP]
         L.orc_kat_hit.argtypes = [VP, DP, DP, C.c_double, C.c_double, C.c_double, DP]
@@ -96,6 +98,19 @@ class OracleScene:
         if st != 0:
             raise RuntimeError(lib().orc_last_error().decode())
         return rgb, {k: getattr(cnt, k) for k in COUNTER_FIELDS}
+
+    def render_moments(self, cam, integrator, seed=1, nthreads=None):
+        """(mean (H,W,3), mean of squares (H,W,3)) of the per-sample radiance, f64."""
+        H = lib().orc_image_height(C.byref(cam))
+        rgb = np.full((H, cam.image_width, 3), np.nan, dtype=np.float64)
+        sq = np.full((H, cam.image_width, 3), np.nan, dtype=np.float64)
+        if nthreads is None:
+            nthreads = os.cpu_count() or 1
+        st = lib().orc_render_moments(self._h, C.byref(cam), integrator, seed, nthreads, 0, H, 1, rgb.ctypes.data,
+                                      sq.ctypes.data, None)
+        if st != 0:
+            raise RuntimeError(lib().orc_last_error().decode())
+        return rgb, sq
 
     def hit(self, origin, direction, time=0.0, tmin=0.001, tmax=float("inf")):
         out = (C.c_double * 12)()

@@ -1,6 +1,5 @@
 """Committed fixtures (tests/golden/, made by scripts/make_golden.py): the oracle must reproduce
 them on CPU; the CUDA path must match them on the GPU without the oracle being present."""
-import json
 import os
 
 import numpy as np
@@ -44,26 +43,4 @@ def test_gpu_probe_matches_golden(book, no):
     assert np.array_equal(ids, gids)
     hit = gids >= 0
     assert np.max(np.abs(t[hit] - gt[hit]) / gt[hit]) <= 1e-5
-    gs.close(); ctx.close()
-
-
-@pytest.mark.gpu
-@pytest.mark.parametrize("book,no", SCENES)
-def test_gpu_mean_radiance_matches_golden(book, no):
-    """Per-channel mean linear radiance within 0.5 % (north star) of the oracle's converged mean —
-    widened only by the Monte-Carlo error of the two estimates where that is larger."""
-    g = json.load(open(os.path.join(GOLD, "radiance_means.json")))[name(book, no)]
-    s = R.BookScene(book, no, overrides=dict(image_width=g["width"], samples_per_pixel=4 * g["spp"], max_depth=g["depth"]))
-    ctx = R.Context(0)
-    gs = ctx.scene(s.desc)
-    acc = ctx.render(gs, s.camera, s.integrator, seed=5).astype(np.float64)
-    lin = acc[..., :3] / acc[..., 3:4]
-    mean = lin.mean(axis=(0, 1))
-    # standard error of the frame mean from the per-pixel spread of two half-renders is not
-    # available for the golden side; bound it by the GPU side's own split-frame estimate
-    acc2 = ctx.render(gs, s.camera, s.integrator, seed=6).astype(np.float64)
-    mean2 = (acc2[..., :3] / acc2[..., 3:4]).mean(axis=(0, 1))
-    mc = np.abs(mean - mean2) / mean
-    rel = np.abs(0.5 * (mean + mean2) - np.array(g["mean"])) / np.array(g["mean"])
-    assert np.all(rel <= np.maximum(0.005, 4.0 * mc + 0.004)), (rel, mc)
     gs.close(); ctx.close()

@@ -1,9 +1,10 @@
 """GPU parity tests proper: the CUDA path (through the C ABI) against the CPU oracle on the same
 scene descriptions.  Gates from BASELINE.json.north_star:
   * probe mode: primary-hit ids bit-exact, t within 1e-5 relative;
-  * converged renders: PSNR >= 40 dB (or the oracle-vs-oracle noise floor at that spp, whichever is
-    lower — two independent Monte-Carlo renders cannot agree better than their own noise) and
-    per-channel mean radiance within 0.5 %.
+  * converged renders: PSNR >= 40 dB and per-channel mean radiance within 0.5 % — gated as written in
+    tests/test_converged_golden.py against committed high-spp oracle images; here, at equal and lower
+    sample counts, the GPU image must be statistically indistinguishable from a second oracle render
+    (PSNR within 1 dB of oracle-vs-oracle, frame mean within 0.5 % or 3 standard errors).
 """
 import numpy as np
 import pytest
@@ -56,10 +57,13 @@ def test_probe_f32_kernel_close(ctx, book, scene_no):
     gs = ctx.scene(s.desc)
     ids, t = ctx.probe(gs, s.camera, 32)
     oids, ot = O.OracleScene(s.desc).probe(s.camera)
-    assert (ids != oids).mean() < 2e-3
+    # measured at full size (tests/golden/probe_f32.json, gated there at twice the measurement): at most
+    # 3e-5 of the ids differ (silhouettes), t within 5e-3 on the r = 1000 ground sphere near the horizon and
+    # within 3e-5 at the 99th percentile; this is the 640-px smoke version of that test
+    assert (ids != oids).mean() < 1e-4
     same = (ids == oids) & (oids >= 0)
     rel = np.abs(t[same] - ot[same]) / ot[same]
-    assert np.median(rel) < 1e-5 and rel.max() < 1e-2
+    assert np.median(rel) < 1e-6 and np.quantile(rel, 0.99) < 6e-5 and rel.max() < 1e-2
 
 
 RENDER_CASES = [
@@ -88,19 +92,22 @@ def test_converged_render_matches_oracle(ctx, book, scene_no, width, spp, depth)
     assert np.allclose(acc[..., 3], spp_eff)
     gpu_lin = acc[..., :3].astype(np.float64) / spp_eff
     o = O.OracleScene(s.desc)
-    a, _ = o.render(s.camera, s.integrator, seed=11)
-    b, _ = o.render(s.camera, s.integrator, seed=12)
+    a, asq = o.render_moments(s.camera, s.integrator, seed=11)
+    b, bsq = o.render_moments(s.camera, s.integrator, seed=12)
     nan_scrub = s.integrator == F.INT_BOOK3
     img_gpu = ctx.resolve(acc, spp_eff)
     img_a, img_b = O.write_color(a, nan_scrub), O.write_color(b, nan_scrub)
     floor = psnr8(img_a, img_b)
     got = psnr8(img_gpu, img_a)
-    assert got >= min(40.0, floor - 1.0), f"PSNR {got:.2f} dB vs oracle noise floor {floor:.2f} dB"
+    # equal sample counts: the GPU image must be as close to an oracle image as a second oracle image is
+    # (1 dB = 26 % in MSE).  The >= 40 dB gate itself is tests/test_converged_golden.py.
+    assert got >= floor - 1.0, f"PSNR {got:.2f} dB vs oracle-vs-oracle {floor:.2f} dB at the same spp"
     ref_mean = 0.5 * (np.nanmean(a, axis=(0, 1)) + np.nanmean(b, axis=(0, 1)))
     gpu_mean = gpu_lin.mean(axis=(0, 1))
-    noise = np.abs(np.nanmean(a, axis=(0, 1)) - np.nanmean(b, axis=(0, 1))) / ref_mean
+    var = np.clip(0.5 * (asq + bsq) - (0.5 * (a + b)) ** 2, 0, None)
+    se = np.sqrt(np.nansum(var, axis=(0, 1)) * (1.0 / spp_eff + 0.5 / spp_eff)) / np.isfinite(a[..., 0]).sum()
     rel = np.abs(gpu_mean - ref_mean) / ref_mean
-    assert np.all(rel <= np.maximum(0.005, 3.0 * noise)), f"mean radiance off by {rel} (oracle self-noise {noise})"
+    assert np.all(rel <= np.maximum(0.005, 3.0 * se / ref_mean)), f"mean radiance off by {rel} (s.e. {se / ref_mean})"
 
 
 def test_resolve_matches_render_io(ctx):

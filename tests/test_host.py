@@ -201,3 +201,46 @@ def test_jpeg_decoder_handles_subsampling_restarts_and_grey(tmp_path):
     p = str(tmp_path / "prog.jpg")
     Image.fromarray(img).save(p, progressive=True)
     assert F.rrth().rrth_load_image(p.encode(), None, None, None, None, 0) == -1       # rejected loudly, not mis-decoded
+
+
+def test_jpeg_decoder_rejects_malformed_files(tmp_path):
+    """A corrupt earthmap.jpg must be an error, not undefined behaviour: Huffman selectors outside the
+    four tables (SOS), component tables longer than their segment (SOF, SOS), truncation anywhere,
+    and random bytes after a valid SOI."""
+    from PIL import Image
+    rng = np.random.default_rng(11)
+    img = rng.integers(0, 255, (24, 40, 3)).astype(np.uint8)
+    good = str(tmp_path / "good.jpg")
+    Image.fromarray(img).save(good, quality=90, subsampling=0)
+    data = bytearray(open(good, "rb").read())
+    load = lambda p: F.rrth().rrth_load_image(p.encode(), None, None, None, None, 0)
+    assert load(good) == 0
+
+    def variant(name, edit):
+        d = bytearray(data)
+        edit(d)
+        p = str(tmp_path / name)
+        open(p, "wb").write(bytes(d))
+        return p
+
+    sos = data.index(b"\xff\xda")
+    sof = data.index(b"\xff\xc0")
+    def bad_selectors(d): d[sos + 6] = 0xF7          # Td = 15, Ta = 7 for the first component
+    def short_sos(d): d[sos + 2:sos + 4] = b"\x00\x04"  # length 4 < 6 + 2 * 3
+    def short_sof(d): d[sof + 2:sof + 4] = b"\x00\x09"  # length 9 < 8 + 3 * 3
+    def many_components(d): d[sof + 9] = 4
+    assert load(variant("sel.jpg", bad_selectors)) == -1
+    assert load(variant("sos.jpg", short_sos)) == -1
+    assert load(variant("sof.jpg", short_sof)) == -1
+    assert load(variant("nc.jpg", many_components)) == -1
+    for cut in (3, sof + 5, sos + 3, sos + 20, len(data) - 40):      # truncated: error or a decode that stays in bounds
+        p = str(tmp_path / f"cut{cut}.jpg")
+        open(p, "wb").write(bytes(data[:cut]))
+        assert load(p) in (0, -1)
+    for k in range(20):                                             # garbage after SOI
+        p = str(tmp_path / f"fuzz{k}.jpg")
+        d = bytearray(data)
+        for pos in rng.integers(2, len(d), 12):
+            d[pos] = int(rng.integers(0, 256))
+        open(p, "wb").write(bytes(d))
+        assert load(p) in (0, -1)
