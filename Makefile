@@ -24,12 +24,15 @@ $(CSRC)/probe64.o: $(CSRC)/probe64.cu $(CSRC)/*.cuh $(CSRC)/*.h include/rrt.h
 	$(NVCC) -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -fmad=false -Xcompiler -fPIC -c $< -o $@
 $(CSRC)/api.o: $(CSRC)/api.cu $(CSRC)/*.cuh $(CSRC)/*.h $(CSRC)/flatten.hpp include/rrt.h
 	$(NVCC) $(NVFLAGS) -c $< -o $@
+# several GPUs behind the C ABI: NCCL reduce / gather of the frame (links libnccl)
+$(CSRC)/multi.o: $(CSRC)/multi.cu $(CSRC)/*.h $(CSRC)/flatten.hpp include/rrt.h
+	$(NVCC) $(NVFLAGS) -c $< -o $@
 $(CSRC)/flatten.o: $(CSRC)/flatten.cpp $(CSRC)/flatten.hpp $(CSRC)/device_types.h include/rrt.h
 	$(NVCC) $(NVFLAGS) -x cu -c $< -o $@
 
 KOBJ := $(CSRC)/kernels_book1.o $(CSRC)/kernels_book2.o $(CSRC)/kernels_book3.o
-$(PKG)/librrt.so: $(CSRC)/kernels.o $(KOBJ) $(CSRC)/probe64.o $(CSRC)/api.o $(CSRC)/flatten.o
-	$(NVCC) -gencode arch=compute_100a,code=sm_100a -shared -o $@ $^ -cudart shared
+$(PKG)/librrt.so: $(CSRC)/kernels.o $(KOBJ) $(CSRC)/probe64.o $(CSRC)/api.o $(CSRC)/multi.o $(CSRC)/flatten.o
+	$(NVCC) -gencode arch=compute_100a,code=sm_100a -shared -o $@ $^ -cudart shared -lnccl
 
 HOST_SRC := $(HOST)/books.cpp $(HOST)/rtw_image.cpp $(HOST)/jpeg_decode.cpp $(HOST)/render_io.cpp
 $(PKG)/librrt_host.so: $(HOST_SRC) $(HOST)/*.hpp include/*.h

@@ -30,13 +30,20 @@ pub struct RrtRenderParams { pub integrator: i32, pub shard_mode: i32, pub rank:
 #[repr(C)] #[derive(Clone, Copy, Default)]
 pub struct RrtStats { pub width: i32, pub height: i32, pub spp_effective: i32, pub kernel_launches: i32,
                       pub paths: f64, pub kernel_ms: f64, pub total_ms: f64, pub h2d_bytes: u64, pub d2h_bytes: u64,
-                      pub n_prims: i32, pub n_bvh_nodes: i32, pub n_media: i32, pub n_lights: i32, pub sm_count: i32, pub kernel_features: i32 }
+                      pub n_prims: i32, pub n_bvh_nodes: i32, pub n_media: i32, pub n_lights: i32, pub sm_count: i32, pub kernel_features: i32,
+                      pub n_devices: i32, pub _pad: i32, pub exchange_ms: f64 }
 #[repr(C)] pub struct RrtCtx { _p: [u8; 0] }
 #[repr(C)] pub struct RrtScene { _p: [u8; 0] }
 
 extern "C" {
     pub fn rrt_init(device: c_int, out: *mut *mut RrtCtx) -> c_int;
     pub fn rrt_shutdown(ctx: *mut RrtCtx);
+    pub fn rrt_init_multi(devices: *const c_int, n_devices: c_int, out: *mut *mut RrtCtx) -> c_int;
+    pub fn rrt_comm_unique_id(id128: *mut u8) -> c_int;
+    pub fn rrt_comm_init(ctx: *mut RrtCtx, id128: *const u8, rank: c_int, world: c_int) -> c_int;
+    pub fn rrt_render_collective(ctx: *mut RrtCtx, scene: *const RrtScene, cam: *const RrtCamera, p: *const RrtRenderParams,
+                                 accum_dev_root: *mut f32, accum_host_root: *mut f32) -> c_int;
+    pub fn rrt_tile_scatter_host(cam: *const RrtCamera, world: c_int, shares: *const *const f32, frame: *mut f32) -> c_int;
     pub fn rrt_set_stream(ctx: *mut RrtCtx, cuda_stream: *mut c_void) -> c_int;
     pub fn rrt_scene_create(ctx: *mut RrtCtx, desc: *const RrtSceneDesc, out: *mut *mut RrtScene) -> c_int;
     pub fn rrt_scene_destroy(scene: *mut RrtScene);

@@ -15,7 +15,8 @@
  *
  * Errors: 0 = ok, negative rrt_status otherwise, text via rrt_last_error() (thread-local),
  * replacing Result<(), String> (src/cuda/mod.rs:342-441).  Never aborts; never falls back to CPU.
- * Threading: blocking calls from one host thread per context; one context = one CUDA device.
+ * Threading: blocking calls from one host thread per context; one context = one CUDA device, or a
+ * group of them (rrt_init_multi) driven by that one thread.
  */
 #ifndef RRT_H
 #define RRT_H
@@ -171,6 +172,11 @@ typedef struct rrt_stats {
                             * spheres, 1 quads, 2 constant media, 3 non-solid textures, 4 Perlin noise,
                             * 5 box leaves (63 = the general instance); a scene runs on the smallest instance covering it.
                             * RRT_KERNEL=full in the environment at rrt_init forces 63 (debugging). */
+  int32_t n_devices;       /* GPUs behind the last call: 1, the size of an rrt_init_multi group, or the communicator's world */
+  int32_t _pad;
+  double exchange_ms;      /* device time of the frame exchange after the kernels (NCCL reduce, or gather of owned tiles
+                            * + scatter into the frame) on the rank that receives it; 0 on one GPU.  With several GPUs
+                            * kernel_ms is the slowest member's kernel and paths counts every member's. */
 } rrt_stats;
 
 typedef struct rrt_ctx rrt_ctx;
@@ -188,6 +194,36 @@ typedef struct rrt_scene rrt_scene;
  *                          being tested ahead of the traversal */
 int rrt_init(int device, rrt_ctx** out);
 void rrt_shutdown(rrt_ctx* ctx);
+
+/* ---- several GPUs of one box -------------------------------------------------------
+ * The reference has one caller, one blocking call (src/main.rs:58-66 -> fn render, src/cuda/mod.rs:342).
+ * Both multi-GPU forms keep that shape: the frame is partitioned inside the library — sample ranges
+ * (params->shard_mode = RRT_SHARD_SAMPLE, the default for a group when RRT_SHARD_NONE is passed) or
+ * interleaved 32x32 tiles (RRT_SHARD_TILE) — the shares are rendered concurrently, and one NCCL exchange
+ * over NVLink brings the frame to the first device: a SUM-reduce of the RGBA-sum frames for sample
+ * ranges, a gather of each rank's OWN tiles (packed back to back; 1/world of the frame per rank, not a
+ * zero-padded full frame) followed by a scatter kernel for tiles.  params->rank / world are ignored.
+ *
+ * (A) one process, n GPUs — what a host binding this header uses:
+ *   rrt_init_multi: a group context over devices[0..n); devices[0] receives the frame.  Every entry
+ *   point takes the group like a plain context: rrt_scene_create uploads to every member,
+ *   rrt_render / rrt_render_frame / rrt_render_device return the complete frame (host, or device memory
+ *   of devices[0]); rrt_probe, rrt_resolve_* and the rrt_kat_* hooks run on devices[0].
+ * (B) one process per GPU (torchrun, MPI): every rank creates a plain context with rrt_init, rank 0 calls
+ *   rrt_comm_unique_id and hands the 128 bytes to the others by whatever means the launcher offers, every
+ *   rank calls rrt_comm_init (collective, as ncclCommInitRank), and then
+ *   rrt_render_collective (collective): renders this rank's share and exchanges.  On rank 0 the frame
+ *   lands in accum_dev_root (device, W*H*4 floats; NULL = library-owned) and, when accum_host_root is not
+ *   NULL, is copied there too; both are ignored on the other ranks. */
+int rrt_init_multi(const int* devices, int n_devices, rrt_ctx** out);
+int rrt_comm_unique_id(uint8_t* id128);
+int rrt_comm_init(rrt_ctx* ctx, const uint8_t* id128, int rank, int world);
+int rrt_render_collective(rrt_ctx* ctx, const rrt_scene* scene, const rrt_camera* cam,
+                          const rrt_render_params* params, float* accum_dev_root, float* accum_host_root);
+/* Host-only mirror of the tile exchange's last step (tests): shares[r] = rank r's compact tiles
+ * (owned 32x32 super tiles back to back, 1024 RGBA pixels each, row-major inside a tile; super tile k
+ * belongs to rank k % world and is its (k / world)-th) -> row-major RGBA frame. */
+int rrt_tile_scatter_host(const rrt_camera* cam, int world, const float* const* shares, float* frame);
 
 /* Launch on the caller's CUDA stream (a cudaStream_t, e.g. torch.cuda.current_stream().cuda_stream)
  * instead of the context's own; NULL restores the library's stream.  The reference has one implicit
@@ -208,7 +244,19 @@ int rrt_image_height(const rrt_camera* cam);
  * (layout of src/render_io.rs:11, src/cuda/mod.rs:330-332).
  *   rrt_render:        accum_host is caller-allocated W*H*4 floats; includes the D2H copy.
  *   rrt_render_device: accum_dev is a device pointer (W*H*4 floats) on this context's GPU; the call
- *                      returns after the kernels completed; nothing leaves HBM. */
+ *                      returns after the kernels completed; nothing leaves HBM.
+ *
+ * Non-finite samples (the one deliberate difference from the reference's accumulation): Camera::render
+ * adds every sample to the pixel (camera.rs:79-83), so a single NaN — a scattering point inside a sphere
+ * light, where sphere.rs:110 takes sqrt of a negative number — makes the whole pixel NaN and write_color
+ * (color.rs:19-27) prints it black.  Here a path ends where its pdf stops being a positive number, a
+ * sample whose radiance is not finite adds nothing to rgb, and .w still counts it; none of the book
+ * scenes produces such a sample (tests/test_book3_sampling.py pins the behaviour on one that does).
+ * In f32 the same rule keeps one overflowing weight among 6e10 paths from blacking out a pixel.
+ *
+ * Reproducibility: per-sample radiance is a pure function of (seed, pixel, sample); frames of the default
+ * schedule differ from run to run in the last bits (float atomics in completion order, see
+ * RRT_DETERMINISTIC above). */
 int rrt_render(rrt_ctx* ctx, const rrt_scene* scene, const rrt_camera* cam,
                const rrt_render_params* params, float* accum_host);
 int rrt_render_device(rrt_ctx* ctx, const rrt_scene* scene, const rrt_camera* cam,

@@ -6,7 +6,7 @@ load the libraries; the first call does, and fails loudly if they are missing.
 """
 from . import _ffi
 from .api import (BookScene, Context, DescBuilder, GpuScene, RrtError, copy_camera, flatten_check,
-                  make_camera, make_overrides, scene_features, shard_plan, shipped_overrides)
+                  make_camera, make_overrides, scene_features, shard_plan, shipped_overrides, tile_scatter_host)
 
 __all__ = ["BookScene", "Context", "DescBuilder", "GpuScene", "RrtError", "copy_camera",
-           "flatten_check", "make_camera", "make_overrides", "scene_features", "shard_plan", "shipped_overrides", "_ffi"]
+           "flatten_check", "make_camera", "make_overrides", "scene_features", "shard_plan", "shipped_overrides", "tile_scatter_host", "_ffi"]

@@ -68,7 +68,8 @@ class Stats(C.Structure):
                 ("paths", c_dbl), ("kernel_ms", c_dbl), ("total_ms", c_dbl),
                 ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
                 ("n_prims", c_int), ("n_bvh_nodes", c_int), ("n_media", c_int), ("n_lights", c_int),
-                ("sm_count", c_int), ("kernel_features", c_int)]
+                ("sm_count", c_int), ("kernel_features", c_int), ("n_devices", c_int), ("_pad", c_int),
+                ("exchange_ms", c_dbl)]
 
 
 class Overrides(C.Structure):
@@ -95,6 +96,11 @@ VP = C.c_void_p
 RRT_SYMBOLS = [
     ("rrt_init", c_int, [c_int, C.POINTER(VP)]),
     ("rrt_shutdown", None, [VP]),
+    ("rrt_init_multi", c_int, [C.POINTER(c_int), c_int, C.POINTER(VP)]),
+    ("rrt_comm_unique_id", c_int, [VP]),
+    ("rrt_comm_init", c_int, [VP, VP, c_int, c_int]),
+    ("rrt_render_collective", c_int, [VP, VP, C.POINTER(Camera), C.POINTER(RenderParams), VP, VP]),
+    ("rrt_tile_scatter_host", c_int, [C.POINTER(Camera), c_int, C.POINTER(VP), VP]),
     ("rrt_set_stream", c_int, [VP, VP]),
     ("rrt_scene_create", c_int, [VP, C.POINTER(SceneDesc), C.POINTER(VP)]),
     ("rrt_scene_destroy", None, [VP]),

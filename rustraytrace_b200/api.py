@@ -224,6 +224,16 @@ def shard_plan(camera, integrator, shard_mode, rank, world, mask=False):
     return out
 
 
+def tile_scatter_host(camera, shares):
+    """rrt_tile_scatter_host (host only): per-rank compact tile buffers (float32, n_owned * 1024 * 4) -> (H, W, 4) frame."""
+    H = F.rrt().rrt_image_height(C.byref(camera))
+    arrs = [np.ascontiguousarray(a, dtype=np.float32) for a in shares]
+    ptrs = (C.c_void_p * len(arrs))(*[a.ctypes.data for a in arrs])
+    frame = np.zeros((H, camera.image_width, 4), dtype=np.float32)
+    _check(F.rrt().rrt_tile_scatter_host(C.byref(camera), len(arrs), ptrs, frame.ctypes.data))
+    return frame
+
+
 class GpuScene:
     def __init__(self, ctx, handle):
         self.ctx, self._handle = ctx, handle
@@ -243,10 +253,40 @@ class GpuScene:
 class Context:
     """One CUDA device (rrt_init).  Raises RrtError(ERR_NO_DEVICE) when there is no GPU."""
 
-    def __init__(self, device=0):
+    def __init__(self, device=0, devices=None):
+        """device: one GPU (rrt_init).  devices=[0, 1, ...]: a group over several GPUs of this box driven by
+        this process (rrt_init_multi); every method then returns the complete frame, exchanged over NCCL."""
         self._h = C.c_void_p()
-        _check(F.rrt().rrt_init(int(device), C.byref(self._h)))
-        self.device = int(device)
+        if devices is not None:
+            arr = (F.c_int * len(devices))(*[int(d) for d in devices])
+            _check(F.rrt().rrt_init_multi(arr, len(devices), C.byref(self._h)))
+            self.device, self.devices = int(devices[0]), [int(d) for d in devices]
+        else:
+            _check(F.rrt().rrt_init(int(device), C.byref(self._h)))
+            self.device, self.devices = int(device), [int(device)]
+
+    # ---- one process per GPU: an NCCL communicator inside the library (rrt_comm_*) -----------------
+    @staticmethod
+    def comm_unique_id():
+        """rrt_comm_unique_id: 128 bytes made on rank 0, to be handed to every rank (bytes)."""
+        buf = (C.c_uint8 * 128)()
+        _check(F.rrt().rrt_comm_unique_id(buf))
+        return bytes(buf)
+
+    def comm_init(self, unique_id, rank, world):
+        """rrt_comm_init (collective): join the communicator as `rank` of `world`."""
+        buf = (C.c_uint8 * 128)(*unique_id)
+        _check(F.rrt().rrt_comm_init(self._h, buf, int(rank), int(world)))
+        self.rank, self.world = int(rank), int(world)
+
+    def render_collective(self, gscene, camera, integrator, seed=1, shard_mode=F.SHARD_SAMPLE, accum_ptr=None, out=None):
+        """rrt_render_collective (collective): this rank's share + the NCCL exchange; on rank 0 the frame goes to
+        device memory `accum_ptr` (None: library-owned) and, if `out` (host (H, W, 4) float32 array) is given, there."""
+        p = self.params(integrator, seed, shard_mode, 0, 1)
+        _check(F.rrt().rrt_render_collective(self._h, gscene._handle, C.byref(camera), C.byref(p),
+                                             C.c_void_p(int(accum_ptr)) if accum_ptr else None,
+                                             out.ctypes.data if out is not None else None))
+        return out
 
     def close(self):
         if self._h:

@@ -16,43 +16,15 @@
 #include "../../include/rrt.h"
 #include "device_types.h"
 #include "flatten.hpp"
+#include "ctx.h"
 #include "kernels.h"
 #include "rng.cuh"
 
 using namespace rrt;
 
 static thread_local std::string g_err;
-static int fail(int st, const std::string& m) { g_err = m; return st; }
-#define CK(call, what)                                                                   \
-  do {                                                                                   \
-    cudaError_t e_ = (call);                                                             \
-    if (e_ != cudaSuccess) return fail(RRT_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e_)); \
-  } while (0)
-
-struct rrt_scene;
-struct rrt_ctx {
-  int device = 0;
-  int sm_count = 0;
-  cudaStream_t stream = nullptr;      // the stream every call launches on
-  cudaStream_t own_stream = nullptr;  // created by rrt_init; `stream` points elsewhere after rrt_set_stream
-  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
-  unsigned int* counter = nullptr;
-  float* accum = nullptr;  // grow-only frame buffer for the host-output entry points
-  size_t accum_floats = 0;
-  rrt_stats stats;
-  bool no_steal = false;              // RRT_NO_STEAL=1: lanes never take over neighbours' samples (debugging / A-B)
-  bool deterministic = false;         // RRT_DETERMINISTIC=1: no stealing, one chunk per tile -> bit-reproducible frames
-  bool force_full_kernel = false;     // RRT_KERNEL=full: always run the SF_ALL render kernel instance (include/rrt.h)
-  std::vector<rrt_scene*> scenes;  // live scenes of this context (released by rrt_shutdown if the caller did not)
-};
-
-struct rrt_scene {
-  rrt_ctx* ctx = nullptr;
-  std::vector<void*> allocs;
-  DevScene dev;
-  int n_nodes = 0, n_prims = 0, n_media = 0, n_lights = 0;
-  uint64_t h2d_bytes = 0;
-};
+int rrt::fail(int st, const std::string& m) { g_err = m; return st; }
+using rrt::fail;
 
 template <typename T>
 static int upload(rrt_scene* sc, const std::vector<T>& v, const T** out) {
@@ -68,99 +40,28 @@ static int upload(rrt_scene* sc, const std::vector<T>& v, const T** out) {
   return RRT_OK;
 }
 
-extern "C" {
+// the device a single-device operation of a group context runs on, and its copy of the scene
+static rrt_ctx* root_of(rrt_ctx* c) { return c && !c->members.empty() ? c->members[0] : c; }
+static const rrt_scene* part0_of(const rrt_scene* sc) { return sc && !sc->parts.empty() ? sc->parts[0] : sc; }
 
-const char* rrt_last_error(void) { return g_err.c_str(); }
-const char* rrt_version(void) { return "rrt-b200 0.1 (sm_100a)"; }
-
-int rrt_init(int device, rrt_ctx** out) {
-  if (!out) return fail(RRT_ERR_INVALID, "rrt_init: out is null");
-  *out = nullptr;
-  int n = 0;
-  cudaError_t e = cudaGetDeviceCount(&n);
-  if (e != cudaSuccess || n == 0) {
-    cudaGetLastError();
-    return fail(RRT_ERR_NO_DEVICE, std::string("cuda init failed: no CUDA device (") +
-                                       (e != cudaSuccess ? cudaGetErrorString(e) : "count 0") +
-                                       "); this library has no CPU fallback");
+// ---- internals shared with multi.cu (ctx.h) -------------------------------------------------------
+void rrt::scene_release(rrt_scene* sc) {
+  for (rrt_scene* part : sc->parts) {
+    if (rrt_ctx* m = part->ctx) {
+      cudaSetDevice(m->device);
+      cudaStreamSynchronize(m->stream);
+      for (size_t i = 0; i < m->scenes.size(); ++i)
+        if (m->scenes[i] == part) { m->scenes.erase(m->scenes.begin() + i); break; }
+    }
+    scene_release(part);
   }
-  if (device < 0 || device >= n) return fail(RRT_ERR_INVALID, "rrt_init: device index out of range");
-  CK(cudaSetDevice(device), "cuda init failed");
-  rrt_ctx* c = new rrt_ctx();
-  std::memset(&c->stats, 0, sizeof c->stats);
-  c->device = device;
-  cudaDeviceProp prop;
-  CK(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties");
-  if (prop.major < 10) {
-    delete c;
-    return fail(RRT_ERR_NO_DEVICE, std::string("device '") + prop.name + "' is not sm_100-class; kernels are built for sm_100a only");
-  }
-  c->sm_count = prop.multiProcessorCount;
-  const char* kv = std::getenv("RRT_KERNEL");
-  c->force_full_kernel = kv && std::strcmp(kv, "full") == 0;
-  c->no_steal = std::getenv("RRT_NO_STEAL") != nullptr;
-  c->deterministic = std::getenv("RRT_DETERMINISTIC") != nullptr;
-  CK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking), "cudaStreamCreate");
-  c->stream = c->own_stream;
-  for (auto& ev : c->ev) CK(cudaEventCreate(&ev), "cudaEventCreate");
-  CK(cudaMalloc(&c->counter, sizeof(unsigned int)), "cudaMalloc(counter)");
-  c->stats.sm_count = c->sm_count;
-  *out = c;
-  return RRT_OK;
-}
-
-static void release_scene_memory(rrt_scene* sc);
-
-void rrt_shutdown(rrt_ctx* c) {
-  if (!c) return;
-  cudaSetDevice(c->device);
-  if (c->stream) cudaStreamSynchronize(c->stream);
-  // scenes the caller still holds: free their device memory now and orphan the handles, so a late
-  // rrt_scene_destroy (e.g. from a garbage collector) stays harmless
-  for (rrt_scene* sc : c->scenes) release_scene_memory(sc);
-  c->scenes.clear();
-  if (c->accum) cudaFree(c->accum);
-  if (c->counter) cudaFree(c->counter);
-  for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
-  if (c->own_stream) cudaStreamDestroy(c->own_stream);
-  delete c;
-}
-
-int rrt_set_stream(rrt_ctx* c, void* stream) {
-  if (!c) return fail(RRT_ERR_INVALID, "rrt_set_stream: ctx is null");
-  cudaSetDevice(c->device);
-  if (c->stream) cudaStreamSynchronize(c->stream);
-  c->stream = stream ? reinterpret_cast<cudaStream_t>(stream) : c->own_stream;
-  return RRT_OK;
-}
-
-static void release_scene_memory(rrt_scene* sc) {
   for (void* p : sc->allocs) cudaFree(p);
   sc->allocs.clear();
   sc->ctx = nullptr;
 }
 
-void rrt_scene_destroy(rrt_scene* sc) {
-  if (!sc) return;
-  if (rrt_ctx* c = sc->ctx) {
-    cudaSetDevice(c->device);
-    cudaStreamSynchronize(c->stream);
-    for (size_t i = 0; i < c->scenes.size(); ++i)
-      if (c->scenes[i] == sc) { c->scenes.erase(c->scenes.begin() + i); break; }
-    release_scene_memory(sc);
-  }
-  delete sc;
-}
-
-int rrt_scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out) {
-  if (!c || !out) return fail(RRT_ERR_INVALID, "rrt_scene_create: null argument");
+int rrt::scene_upload(rrt_ctx* c, const FlatScene& F, rrt_scene** out) {
   *out = nullptr;
-  FlatScene F;
-  std::string err;
-  int st = flatten_scene(desc, F, err);
-  if (st != RRT_OK) return fail(st, "scene flatten failed: " + err);
-  if (F.bvh_depth >= RRT_STACK)   // the traversal stack holds one entry per level (intersect.cuh)
-    return fail(RRT_ERR_UNSUPPORTED, "BVH depth " + std::to_string(F.bvh_depth) + " exceeds the traversal stack (" + std::to_string(RRT_STACK) + ")");
   CK(cudaSetDevice(c->device), "cudaSetDevice");
   rrt_scene* sc = new rrt_scene();
   sc->ctx = c;
@@ -175,7 +76,7 @@ int rrt_scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out) {
       (rc = upload(sc, F.images, &D.images)) || (rc = upload(sc, F.texels, &texels)) ||
       (rc = upload(sc, F.perlins, &D.perlins)) || (rc = upload(sc, F.media, &D.media)) ||
       (rc = upload(sc, F.lights, &D.lights))) {
-    rrt_scene_destroy(sc);
+    scene_release(sc); delete sc;
     return rc;
   }
   D.texels = texels;
@@ -187,25 +88,15 @@ int rrt_scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out) {
   D.n_lights = (int)F.lights.size();
   D.has_motion = F.has_motion;
   D.features = F.features;
-  if (D.n_media > 5) { rrt_scene_destroy(sc); return fail(RRT_ERR_UNSUPPORTED, "more than 5 constant media"); }
   sc->n_nodes = D.n_nodes; sc->n_prims = D.n_prims; sc->n_media = D.n_media; sc->n_lights = D.n_lights;
-  cudaError_t e = cudaStreamSynchronize(c->stream);  // host vectors die at return
-  if (e != cudaSuccess) { rrt_scene_destroy(sc); return fail(RRT_ERR_CUDA, std::string("scene upload: ") + cudaGetErrorString(e)); }
-  c->stats.h2d_bytes = sc->h2d_bytes;
-  c->stats.n_prims = sc->n_prims; c->stats.n_bvh_nodes = sc->n_nodes;
-  c->stats.n_media = sc->n_media; c->stats.n_lights = sc->n_lights;
+  cudaError_t e = cudaStreamSynchronize(c->stream);  // the host vectors die when the caller returns
+  if (e != cudaSuccess) { scene_release(sc); delete sc; return fail(RRT_ERR_CUDA, std::string("scene upload: ") + cudaGetErrorString(e)); }
   c->scenes.push_back(sc);
   *out = sc;
   return RRT_OK;
 }
 
-int rrt_image_height(const rrt_camera* cam) {
-  if (!cam || !(cam->aspect_ratio > 0.0)) return 0;
-  int h = (int)((double)cam->image_width / cam->aspect_ratio);
-  return h < 1 ? 1 : h;
-}
-
-static int check_camera(const rrt_camera* cam, const rrt_render_params* p) {
+int rrt::check_camera(const rrt_camera* cam, const rrt_render_params* p) {
   if (!cam) return fail(RRT_ERR_INVALID, "camera is null");
   if (cam->image_width < 1 || cam->image_width > 65536 || !(cam->aspect_ratio > 0.0))
     return fail(RRT_ERR_INVALID, "camera: image_width/aspect_ratio out of range");
@@ -222,6 +113,9 @@ static int check_camera(const rrt_camera* cam, const rrt_render_params* p) {
   }
   return RRT_OK;
 }
+using rrt::check_camera;
+
+int rrt::owned_super_tiles(int n_super, int rank, int world) { return rank < n_super ? (n_super - rank + world - 1) / world : 0; }
 
 // This rank's share of the frame: which 32x32 super tiles and which sample range.
 // Pure host arithmetic, shared by rrt_render_device and rrt_shard_plan.
@@ -247,7 +141,7 @@ static void plan_work(const rrt_camera* cam, const rrt_render_params* p, DevWork
   W.stiles_x = (Wd + 31) / 32; W.stiles_y = (H + 31) / 32;
   const int n_super = W.stiles_x * W.stiles_y;
   const int tw = p->shard_mode == RRT_SHARD_TILE ? W.world : 1, tr = p->shard_mode == RRT_SHARD_TILE ? W.rank : 0;
-  const int my_super = tr < n_super ? (n_super - tr + tw - 1) / tw : 0;
+  const int my_super = rrt::owned_super_tiles(n_super, tr, tw);
   W.n_tiles = my_super * 32;
   W.tiles_x = W.stiles_x * 4;
   my_pixels = 0;
@@ -257,12 +151,8 @@ static void plan_work(const rrt_camera* cam, const rrt_render_params* p, DevWork
   }
 }
 
-int rrt_render_device(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, const rrt_render_params* p,
-                      float* accum_dev) {
-  if (!c || !sc || !p || !accum_dev) return fail(RRT_ERR_INVALID, "rrt_render_device: null argument");
-  if (sc->ctx != c) return fail(RRT_ERR_INVALID, "scene belongs to another (or a shut down) context");
-  int rc = check_camera(cam, p);
-  if (rc) return rc;
+int rrt::render_enqueue(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, const rrt_render_params* p, float* dst_dev,
+                        bool compact, ShareInfo* info) {
   CK(cudaSetDevice(c->device), "cudaSetDevice");
   RenderArgs A;
   std::memset(&A, 0, sizeof A);
@@ -270,8 +160,9 @@ int rrt_render_device(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, co
   double my_pixels = 0;
   plan_work(cam, p, A.W, A.cam, my_pixels);
   DevWork& W = A.W;
-  const int Wd = W.width, H = W.height, spp_eff = W.spp_eff;
+  const int Wd = W.width, H = W.height;
   const int n_samples = W.s_end - W.s_begin;
+  W.compact = compact && p->shard_mode == RRT_SHARD_TILE ? 1 : 0;
 
   const RenderVariant* variant = select_render_variant(p->integrator, sc->dev.features, c->force_full_kernel);
   // Sample stealing (render_kernel.cuh) pays wherever path cost varies inside a warp (C1 +20 %, C2/C3a
@@ -293,13 +184,14 @@ int rrt_render_device(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, co
   }
   W.chunks = (int)chunks;
   W.atomic_accum = chunks > 1 ? 1 : 0;
-  A.accum = reinterpret_cast<float4*>(accum_dev);
+  A.accum = reinterpret_cast<float4*>(dst_dev);
   A.counter = c->counter;
 
   CK(cudaEventRecord(c->ev[0], c->stream), "cudaEventRecord");
   CK(cudaMemsetAsync(c->counter, 0, sizeof(unsigned int), c->stream), "cudaMemsetAsync(counter)");
-  if (W.atomic_accum || p->shard_mode == RRT_SHARD_TILE || n_samples <= 0)
-    CK(cudaMemsetAsync(accum_dev, 0, (size_t)Wd * H * 4 * sizeof(float), c->stream), "cudaMemsetAsync(accum)");
+  const size_t dst_floats = W.compact ? (size_t)(W.n_tiles / 32) * 1024 * 4 : (size_t)Wd * H * 4;
+  if (W.atomic_accum || (p->shard_mode == RRT_SHARD_TILE && !W.compact) || n_samples <= 0)
+    CK(cudaMemsetAsync(dst_dev, 0, dst_floats * sizeof(float), c->stream), "cudaMemsetAsync(accum)");
   int launches = 0;
   CK(cudaEventRecord(c->ev[1], c->stream), "cudaEventRecord");
   if (W.n_tiles > 0 && n_samples > 0) {
@@ -307,38 +199,222 @@ int rrt_render_device(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, co
     launches = 1;
   }
   CK(cudaEventRecord(c->ev[2], c->stream), "cudaEventRecord");
-  CK(cudaStreamSynchronize(c->stream), "render kernel failed");
+  if (info) {
+    info->width = Wd; info->height = H; info->spp_eff = W.spp_eff; info->n_samples = std::max(0, n_samples);
+    info->launches = launches; info->features = launches ? variant->features : -1; info->pixels = my_pixels;
+    info->n_super = W.n_tiles / 32;
+  }
+  return RRT_OK;
+}
+
+void rrt::stats_from_share(rrt_ctx* c, const rrt_scene* sc, const ShareInfo& s) {
   float kms = 0, tms = 0;
   cudaEventElapsedTime(&kms, c->ev[1], c->ev[2]);
   cudaEventElapsedTime(&tms, c->ev[0], c->ev[2]);
   rrt_stats& st = c->stats;
-  st.width = Wd; st.height = H; st.spp_effective = spp_eff;
-  st.kernel_launches = launches;
-  st.paths = my_pixels * (double)std::max(0, n_samples);
+  st.width = s.width; st.height = s.height; st.spp_effective = s.spp_eff;
+  st.kernel_launches = s.launches;
+  st.paths = s.pixels * (double)s.n_samples;
   st.kernel_ms = kms; st.total_ms = tms;
+  st.exchange_ms = 0; st.n_devices = 1;
   st.d2h_bytes = 0;
   st.n_prims = sc->n_prims; st.n_bvh_nodes = sc->n_nodes; st.n_media = sc->n_media; st.n_lights = sc->n_lights;
   st.sm_count = c->sm_count;
-  st.kernel_features = launches ? variant->features : -1;
+  st.kernel_features = s.features;
+}
+
+int rrt::ensure_floats(float** buf, size_t* have, size_t floats, const char* what) {
+  if (*have >= floats) return RRT_OK;
+  if (*buf) { cudaFree(*buf); *buf = nullptr; *have = 0; }
+  CK(cudaMalloc(buf, std::max<size_t>(floats, 4) * sizeof(float)), what);
+  *have = floats;
   return RRT_OK;
 }
 
-static int ensure_accum(rrt_ctx* c, size_t floats) {
-  if (c->accum_floats >= floats) return RRT_OK;
-  if (c->accum) { cudaFree(c->accum); c->accum = nullptr; c->accum_floats = 0; }
-  CK(cudaMalloc(&c->accum, floats * sizeof(float)), "cudaMalloc(accum)");
-  c->accum_floats = floats;
+extern "C" {
+
+const char* rrt_last_error(void) { return g_err.c_str(); }
+const char* rrt_version(void) { return "rrt-b200 0.1 (sm_100a)"; }
+
+static int init_device_ctx(int device, rrt_ctx** out) {
+  CK(cudaSetDevice(device), "cuda init failed");
+  rrt_ctx* c = new rrt_ctx();
+  std::memset(&c->stats, 0, sizeof c->stats);
+  c->device = device;
+  cudaDeviceProp prop;
+  cudaError_t e = cudaGetDeviceProperties(&prop, device);
+  if (e != cudaSuccess) { delete c; return fail(RRT_ERR_CUDA, std::string("cudaGetDeviceProperties: ") + cudaGetErrorString(e)); }
+  if (prop.major < 10) {
+    delete c;
+    return fail(RRT_ERR_NO_DEVICE, std::string("device '") + prop.name + "' is not sm_100-class; kernels are built for sm_100a only");
+  }
+  c->sm_count = prop.multiProcessorCount;
+  const char* kv = std::getenv("RRT_KERNEL");
+  c->force_full_kernel = kv && std::strcmp(kv, "full") == 0;
+  c->no_steal = std::getenv("RRT_NO_STEAL") != nullptr;
+  c->deterministic = std::getenv("RRT_DETERMINISTIC") != nullptr;
+  e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
+  c->stream = c->own_stream;
+  for (auto& ev : c->ev) if (e == cudaSuccess) e = cudaEventCreate(&ev);
+  if (e == cudaSuccess) e = cudaMalloc(&c->counter, sizeof(unsigned int));
+  if (e != cudaSuccess) { rrt_shutdown(c); return fail(RRT_ERR_CUDA, std::string("cuda init failed: ") + cudaGetErrorString(e)); }
+  c->stats.sm_count = c->sm_count;
+  c->stats.n_devices = 1;
+  *out = c;
+  return RRT_OK;
+}
+
+static int device_count(int* n) {
+  *n = 0;
+  cudaError_t e = cudaGetDeviceCount(n);
+  if (e != cudaSuccess || *n == 0) {
+    cudaGetLastError();
+    return fail(RRT_ERR_NO_DEVICE, std::string("cuda init failed: no CUDA device (") +
+                                       (e != cudaSuccess ? cudaGetErrorString(e) : "count 0") +
+                                       "); this library has no CPU fallback");
+  }
+  return RRT_OK;
+}
+
+int rrt_init(int device, rrt_ctx** out) {
+  if (!out) return fail(RRT_ERR_INVALID, "rrt_init: out is null");
+  *out = nullptr;
+  int n = 0, rc = device_count(&n);
+  if (rc) return rc;
+  if (device < 0 || device >= n) return fail(RRT_ERR_INVALID, "rrt_init: device index out of range");
+  return init_device_ctx(device, out);
+}
+
+int rrt_init_multi(const int* devices, int n_devices, rrt_ctx** out) {
+  if (!out || !devices) return fail(RRT_ERR_INVALID, "rrt_init_multi: null argument");
+  *out = nullptr;
+  if (n_devices < 1 || n_devices > RRT_MAX_WORLD) return fail(RRT_ERR_INVALID, "rrt_init_multi: between 1 and 64 devices");
+  int n = 0, rc = device_count(&n);
+  if (rc) return rc;
+  for (int i = 0; i < n_devices; ++i) {
+    if (devices[i] < 0 || devices[i] >= n) return fail(RRT_ERR_INVALID, "rrt_init_multi: device index out of range");
+    for (int j = 0; j < i; ++j) if (devices[j] == devices[i]) return fail(RRT_ERR_INVALID, "rrt_init_multi: device listed twice");
+  }
+  rrt_ctx* g = new rrt_ctx();
+  std::memset(&g->stats, 0, sizeof g->stats);
+  g->device = devices[0];
+  for (int i = 0; i < n_devices; ++i) {
+    rrt_ctx* m = nullptr;
+    if ((rc = init_device_ctx(devices[i], &m))) { rrt_shutdown(g); return rc; }
+    m->group = g;
+    g->members.push_back(m);
+  }
+  if ((rc = rrt::multi_comm_init_all(g, devices))) { rrt_shutdown(g); return rc; }
+  g->sm_count = g->members[0]->sm_count;
+  g->stats.sm_count = g->sm_count;
+  g->stats.n_devices = n_devices;
+  *out = g;
+  return RRT_OK;
+}
+
+void rrt_shutdown(rrt_ctx* c) {
+  if (!c) return;
+  if (!c->members.empty() || c->group == nullptr) {
+    // scenes the caller still holds: free their device memory now and orphan the handles, so a late
+    // rrt_scene_destroy (e.g. from a garbage collector) stays harmless
+    for (rrt_scene* sc : c->scenes) rrt::scene_release(sc);
+    c->scenes.clear();
+  }
+  if (!c->members.empty()) {  // a group: its members hold the devices
+    for (rrt_ctx* m : c->members) { m->group = nullptr; rrt_shutdown(m); }
+    c->members.clear();
+    delete c;
+    return;
+  }
+  cudaSetDevice(c->device);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  rrt::comm_release(c);
+  for (rrt_scene* sc : c->scenes) rrt::scene_release(sc);
+  c->scenes.clear();
+  if (c->accum) cudaFree(c->accum);
+  if (c->share) cudaFree(c->share);
+  if (c->staging) cudaFree(c->staging);
+  if (c->counter) cudaFree(c->counter);
+  for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
+  if (c->own_stream) cudaStreamDestroy(c->own_stream);
+  delete c;
+}
+
+int rrt_set_stream(rrt_ctx* c, void* stream) {
+  if (!c) return fail(RRT_ERR_INVALID, "rrt_set_stream: ctx is null");
+  if (!c->members.empty()) return fail(RRT_ERR_INVALID, "rrt_set_stream: a multi-device context launches on its own streams");
+  cudaSetDevice(c->device);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  c->stream = stream ? reinterpret_cast<cudaStream_t>(stream) : c->own_stream;
+  return RRT_OK;
+}
+
+void rrt_scene_destroy(rrt_scene* sc) {
+  if (!sc) return;
+  if (rrt_ctx* c = sc->ctx) {
+    if (c->members.empty()) {
+      cudaSetDevice(c->device);
+      cudaStreamSynchronize(c->stream);
+    }
+    for (size_t i = 0; i < c->scenes.size(); ++i)
+      if (c->scenes[i] == sc) { c->scenes.erase(c->scenes.begin() + i); break; }
+  }
+  rrt::scene_release(sc);
+  for (rrt_scene* part : sc->parts) delete part;
+  delete sc;
+}
+
+int rrt_scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out) {
+  if (!c || !out) return fail(RRT_ERR_INVALID, "rrt_scene_create: null argument");
+  *out = nullptr;
+  FlatScene F;
+  std::string err;
+  int st = flatten_scene(desc, F, err);
+  if (st != RRT_OK) return fail(st, "scene flatten failed: " + err);
+  if (F.bvh_depth >= RRT_STACK)   // the traversal stack holds one entry per level (intersect.cuh)
+    return fail(RRT_ERR_UNSUPPORTED, "BVH depth " + std::to_string(F.bvh_depth) + " exceeds the traversal stack (" + std::to_string(RRT_STACK) + ")");
+  if (F.media.size() > 5) return fail(RRT_ERR_UNSUPPORTED, "more than 5 constant media");
+  rrt_scene* sc = nullptr;
+  int rc = c->members.empty() ? rrt::scene_upload(c, F, &sc) : rrt::multi_scene_create(c, F, &sc);
+  if (rc) return rc;
+  const rrt_scene* p0 = part0_of(sc);
+  c->stats.h2d_bytes = sc->h2d_bytes;
+  c->stats.n_prims = p0->n_prims; c->stats.n_bvh_nodes = p0->n_nodes;
+  c->stats.n_media = p0->n_media; c->stats.n_lights = p0->n_lights;
+  *out = sc;
+  return RRT_OK;
+}
+
+int rrt_image_height(const rrt_camera* cam) {
+  if (!cam || !(cam->aspect_ratio > 0.0)) return 0;
+  int h = (int)((double)cam->image_width / cam->aspect_ratio);
+  return h < 1 ? 1 : h;
+}
+
+int rrt_render_device(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, const rrt_render_params* p,
+                      float* accum_dev) {
+  if (!c || !sc || !p || !accum_dev) return fail(RRT_ERR_INVALID, "rrt_render_device: null argument");
+  if (sc->ctx != c) return fail(RRT_ERR_INVALID, "scene belongs to another (or a shut down) context");
+  int rc = check_camera(cam, p);
+  if (rc) return rc;
+  if (!c->members.empty()) return rrt::multi_render(c, sc, cam, p, accum_dev, nullptr);
+  rrt::ShareInfo info;
+  if ((rc = rrt::render_enqueue(c, sc, cam, p, accum_dev, false, &info))) return rc;
+  CK(cudaStreamSynchronize(c->stream), "render kernel failed");
+  rrt::stats_from_share(c, sc, info);
   return RRT_OK;
 }
 
 int rrt_render(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, const rrt_render_params* p, float* accum_host) {
-  if (!c || !accum_host) return fail(RRT_ERR_INVALID, "rrt_render: null argument");
+  if (!c || !sc || !p || !accum_host) return fail(RRT_ERR_INVALID, "rrt_render: null argument");
+  if (sc->ctx != c) return fail(RRT_ERR_INVALID, "scene belongs to another (or a shut down) context");
   int rc = check_camera(cam, p);
   if (rc) return rc;
+  if (!c->members.empty()) return rrt::multi_render(c, sc, cam, p, nullptr, accum_host);
   CK(cudaSetDevice(c->device), "cudaSetDevice");
   const int H = rrt_image_height(cam);
   const size_t floats = (size_t)cam->image_width * H * 4;
-  if ((rc = ensure_accum(c, floats))) return rc;
+  if ((rc = rrt::ensure_floats(&c->accum, &c->accum_floats, floats, "cudaMalloc(accum)"))) return rc;
   if ((rc = rrt_render_device(c, sc, cam, p, c->accum))) return rc;
   CK(cudaMemcpyAsync(accum_host, c->accum, floats * sizeof(float), cudaMemcpyDeviceToHost, c->stream), "accum read-back");
   CK(cudaEventRecord(c->ev[3], c->stream), "cudaEventRecord");
@@ -366,6 +442,11 @@ int rrt_probe(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, int precis
   if (!c || !sc || !prim_id || !t) return fail(RRT_ERR_INVALID, "rrt_probe: null argument");
   if (precision != 32 && precision != 64) return fail(RRT_ERR_INVALID, "rrt_probe: precision must be 32 or 64");
   if (sc->ctx != c) return fail(RRT_ERR_INVALID, "scene belongs to another (or a shut down) context");
+  if (!c->members.empty()) {   // one ray per pixel: the first device of a group does it alone
+    int rc0 = rrt_probe(root_of(c), part0_of(sc), cam, precision, prim_id, t);
+    c->stats.kernel_launches = 1;
+    return rc0;
+  }
   int rc = check_camera(cam, nullptr);
   if (rc) return rc;
   CK(cudaSetDevice(c->device), "cudaSetDevice");
@@ -391,6 +472,7 @@ int rrt_probe(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, int precis
 
 int rrt_resolve_rgb8_device(rrt_ctx* c, const float* accum_dev, int width, int height, int spp, uint8_t* rgb_dev) {
   if (!c || !accum_dev || !rgb_dev || width < 1 || height < 1) return fail(RRT_ERR_INVALID, "rrt_resolve_rgb8_device: bad argument");
+  if (!c->members.empty()) return rrt_resolve_rgb8_device(root_of(c), accum_dev, width, height, spp, rgb_dev);
   CK(cudaSetDevice(c->device), "cudaSetDevice");
   CK(launch_resolve(accum_dev, width * height, spp, rgb_dev, c->stream), "kernel launch failed");
   CK(cudaStreamSynchronize(c->stream), "resolve kernel failed");
@@ -400,9 +482,10 @@ int rrt_resolve_rgb8_device(rrt_ctx* c, const float* accum_dev, int width, int h
 
 int rrt_resolve_rgb8(rrt_ctx* c, const float* accum_host, int width, int height, int spp, uint8_t* rgb_host) {
   if (!c || !accum_host || !rgb_host || width < 1 || height < 1) return fail(RRT_ERR_INVALID, "rrt_resolve_rgb8: bad argument");
+  if (!c->members.empty()) return rrt_resolve_rgb8(root_of(c), accum_host, width, height, spp, rgb_host);
   CK(cudaSetDevice(c->device), "cudaSetDevice");
   size_t n = (size_t)width * height;
-  int rc = ensure_accum(c, n * 4);
+  int rc = rrt::ensure_floats(&c->accum, &c->accum_floats, n * 4, "cudaMalloc(accum)");
   if (rc) return rc;
   unsigned char* rgb = nullptr;
   CK(cudaMalloc(&rgb, n * 3), "cudaMalloc(rgb)");
@@ -466,6 +549,7 @@ int rrt_kat_light(rrt_ctx* c, const rrt_scene* sc, int n, const double* origin, 
   if (!c || !sc || n < 0 || !origin || !dir || !u || !pdf_each || !pdf_list || !random_dir)
     return fail(RRT_ERR_INVALID, "rrt_kat_light: null argument");
   if (sc->ctx != c) return fail(RRT_ERR_INVALID, "scene belongs to another (or a shut down) context");
+  if (!c->members.empty()) return rrt_kat_light(root_of(c), part0_of(sc), n, origin, dir, u, pdf_each, pdf_list, random_dir);
   if (n == 0) return RRT_OK;
   CK(cudaSetDevice(c->device), "cudaSetDevice");
   const int nl = sc->n_lights;
@@ -499,6 +583,7 @@ int rrt_kat_light(rrt_ctx* c, const rrt_scene* sc, int n, const double* origin, 
 int rrt_kat_rng(rrt_ctx* c, uint64_t seed, uint32_t pixel, uint32_t sample0, uint32_t bounce, uint32_t block, int n,
                 uint32_t* raw4, float* uniform5) {
   if (!c || n < 0 || (!raw4 && !uniform5)) return fail(RRT_ERR_INVALID, "rrt_kat_rng: bad argument");
+  if (!c->members.empty()) return rrt_kat_rng(root_of(c), seed, pixel, sample0, bounce, block, n, raw4, uniform5);
   if (n == 0) return RRT_OK;
   CK(cudaSetDevice(c->device), "cudaSetDevice");
   uint32_t* draw = nullptr; float* du = nullptr;

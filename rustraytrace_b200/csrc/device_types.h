@@ -184,6 +184,8 @@ struct DevWork {
   int spp_eff;
   unsigned seed_lo, seed_hi;
   int atomic_accum;     // chunks > 1: accumulate with red.add
+  int compact;          // tile sharding for a gather: accum holds this rank's super tiles back to back
+                        //   (1024 float4 each, row-major inside the tile) instead of a full frame
 };
 
 }  // namespace rrt

@@ -55,6 +55,16 @@ __global__ void resolve_kernel(const float4* __restrict__ accum, int n, int spp,
   }
 }
 
+// Tile exchange: super tile k = (y / 32) * stiles_x + x / 32 belongs to rank k % world and is that rank's
+// (k / world)-th; one float4 per pixel, coalesced on both sides (a warp reads one tile row).
+__global__ void tile_scatter_kernel(const __grid_constant__ TileScatterArgs A) {
+  const int x = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
+  if (x >= A.width || y >= A.height) return;
+  const int k = (y >> 5) * A.stiles_x + (x >> 5);
+  const int r = k % A.world, j = k / A.world;
+  A.frame[(size_t)y * A.width + x] = A.staging[(size_t)A.off[r] + (size_t)j * 1024 + (y & 31) * 32 + (x & 31)];
+}
+
 // ------------------------------------------------------------------------------------------------
 // known-answer hooks: the DEVICE code of the book-3 light sampling (shade.cuh light_pdf / light_random,
 // = quad.rs:93-107, sphere.rs:102-122, hittable_list.rs:60-75) and of the sampling RNG (rng.cuh), driven
@@ -93,6 +103,11 @@ __global__ void kat_rng_kernel(unsigned k0, unsigned k1, unsigned pixel, unsigne
 
 // ------------------------------------------------------------------------------------------------
 // launchers (host)
+cudaError_t launch_tile_scatter(const TileScatterArgs& A, cudaStream_t st) {
+  dim3 block(32, 8), grid((A.width + 31) / 32, (A.height + 7) / 8);
+  tile_scatter_kernel<<<grid, block, 0, st>>>(A);
+  return cudaGetLastError();
+}
 cudaError_t launch_kat_light(const KatLightArgs& A, cudaStream_t st) {
   if (A.n <= 0) return cudaSuccess;
   kat_light_kernel<<<(A.n + 127) / 128, 128, 0, st>>>(A);

@@ -72,6 +72,15 @@ cudaError_t launch_render(const RenderVariant* v, bool steal, const RenderArgs& 
 int render_blocks_per_sm(const RenderVariant* v, bool steal);
 cudaError_t launch_probe(const ProbeArgs& A, int precision, cudaStream_t st);
 cudaError_t launch_probe64(const ProbeArgs& A, cudaStream_t st);  // probe64.cu (-fmad=false)
+// Tile exchange, last step on the receiving rank: every rank's packed super tiles (rank-major in
+// `staging`, rank r starting at float4 offset off[r]) -> the row-major frame.
+struct TileScatterArgs {
+  const float4* staging;
+  float4* frame;
+  int width, height, stiles_x, world;
+  unsigned off[64];
+};
+cudaError_t launch_tile_scatter(const TileScatterArgs& A, cudaStream_t st);
 cudaError_t launch_kat_light(const KatLightArgs& A, cudaStream_t st);
 cudaError_t launch_kat_rng(unsigned k0, unsigned k1, unsigned pixel, unsigned sample0, unsigned bounce, unsigned block, int n,
                            uint32_t* raw4, float* u5, cudaStream_t st);

@@ -312,9 +312,12 @@ render_kernel(const __grid_constant__ RenderArgs A) {
     const int s0 = W.s_begin + (int)(((long long)n_samples * chunk) / W.chunks);
     const int s1 = W.s_begin + (int)(((long long)n_samples * (chunk + 1)) / W.chunks);
 
+    // where this pixel's sums go: the frame, or (tile sharding for a gather) this rank's packed super tiles
+    const size_t out_idx = W.compact ? (size_t)(tile >> 5) * 1024 + (size_t)(((tile & 31) >> 2) * 4 + (lane >> 3)) * 32 + ((tile & 3) * 8 + (lane & 7))
+                                     : (size_t)py * W.width + px;
     if (W.max_depth <= 0) {  // ray_color(r, depth <= 0) is black for every sample (camera.rs:185-187; b1 :183-185)
       if (valid) {
-        float4* dst = A.accum + (size_t)py * W.width + px;
+        float4* dst = A.accum + out_idx;
         if (W.atomic_accum) atomicAdd(&dst->w, (float)(s1 - s0));
         else *dst = make_float4(0.0f, 0.0f, 0.0f, (float)(s1 - s0));
       }
@@ -385,7 +388,7 @@ render_kernel(const __grid_constant__ RenderArgs A) {
       sum = sum + V3f(sh_sum[0][threadIdx.x], sh_sum[1][threadIdx.x], sh_sum[2][threadIdx.x]);
     }
     if (valid) {
-      float4* dst = A.accum + (size_t)py * W.width + px;
+      float4* dst = A.accum + out_idx;
       float cnt = (float)(s1 - s0);
       if (W.atomic_accum) {
         atomicAdd(&dst->x, sum.x); atomicAdd(&dst->y, sum.y); atomicAdd(&dst->z, sum.z); atomicAdd(&dst->w, cnt);

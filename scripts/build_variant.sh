@@ -13,8 +13,9 @@ nvcc $F --use_fast_math "$@" -c $C/kernels.cu -o $tmp/kernels.o &
 for b in 1 2 3; do nvcc $F --use_fast_math "$@" -c $C/kernels_book$b.cu -o $tmp/kernels_book$b.o & done
 nvcc $F -fmad=false "$@" -c $C/probe64.cu -o $tmp/probe64.o &
 nvcc $F --use_fast_math "$@" -c $C/api.cu -o $tmp/api.o &
+nvcc $F --use_fast_math "$@" -c $C/multi.cu -o $tmp/multi.o &
 nvcc $F --use_fast_math "$@" -x cu -c $C/flatten.cpp -o $tmp/flatten.o &
 wait
-nvcc -gencode arch=compute_100a,code=sm_100a -shared -o $out/librrt_$name.so $tmp/kernels.o $tmp/kernels_book1.o $tmp/kernels_book2.o $tmp/kernels_book3.o $tmp/probe64.o $tmp/api.o $tmp/flatten.o -cudart shared 
+nvcc -gencode arch=compute_100a,code=sm_100a -shared -o $out/librrt_$name.so $tmp/kernels.o $tmp/kernels_book1.o $tmp/kernels_book2.o $tmp/kernels_book3.o $tmp/probe64.o $tmp/api.o $tmp/multi.o $tmp/flatten.o -cudart shared -lnccl
 rm -rf $tmp
 echo built $out/librrt_$name.so

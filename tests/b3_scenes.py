@@ -100,18 +100,32 @@ def random_b3(seed, width=48, spp=1024):
     lq = b.quad((-1.5, 5.5, -1.5), (3, 0, 0), (0, 0, 3), lightm)                    # n = -y: emits downward
     ls = b.sphere((float(rng.uniform(-4, -2)), float(rng.uniform(1, 3)), float(rng.uniform(-3, 0))), 0.6, lightm)
     objs += [lq, ls]
+    lc = np.array(b.h[ls].a)
+
+    def clear_of_light(c, r):
+        """Nothing may reach into the sphere light: a scattering point inside it has cos_theta_max = NaN
+        (sphere.rs:110), which the reference turns into a black pixel and the GPU into a dropped sample."""
+        return np.linalg.norm(np.array(c) - lc) > r + 0.6 + 0.15
+
     for _ in range(int(rng.integers(3, 7))):
-        c = (float(rng.uniform(-4, 4)), float(rng.uniform(-1.2, 2.5)), float(rng.uniform(-4, 3)))
-        r = float(rng.uniform(0.4, 1.1))
+        while True:
+            c = (float(rng.uniform(-4, 4)), float(rng.uniform(-1.2, 2.5)), float(rng.uniform(-4, 3)))
+            r = float(rng.uniform(0.4, 1.1))
+            if clear_of_light(c, r + 0.5):    # + the moving spheres' travel
+                break
         if rng.integers(3) == 0:
             objs.append(b.sphere(c, r, pick(), center2=(c[0], c[1] + float(rng.uniform(0.1, 0.5)), c[2])))
         else:
             objs.append(b.sphere(c, r, pick()))
     lo = rng.uniform(-3, 1, 3)
+    while not clear_of_light(lo, 1.3):
+        lo = rng.uniform(-3, 1, 3)
     bx = inward_box(b, 0.7, pick())
     objs.append(b.translate(b.rotate_y(b.list(bx), float(rng.uniform(-40, 40))), tuple(lo)))
-    objs.append(b.medium(b.sphere((float(rng.uniform(-2, 2)), 0.5, float(rng.uniform(-2, 2))), 1.3, glass),
-                         float(rng.uniform(0.3, 1.5)), phase))
+    mc = (float(rng.uniform(-2, 2)), 0.5, float(rng.uniform(-2, 2)))
+    while not clear_of_light(mc, 1.3):
+        mc = (float(rng.uniform(-2, 2)), 0.5, float(rng.uniform(-2, 2)))
+    objs.append(b.medium(b.sphere(mc, 1.3, glass), float(rng.uniform(0.3, 1.5)), phase))
     world = b.bvh(objs) if rng.integers(2) else b.list(objs)
     empty = b.material(F.M_EMPTY)
     lights = b.list([b.quad((1.5, 5.5, 1.5), (-3, 0, 0), (0, 0, -3), empty), b.sphere(tuple(b.h[ls].a), 0.6, empty)])

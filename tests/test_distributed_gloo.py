@@ -60,6 +60,45 @@ def test_two_rank_shares_reduce_to_the_full_frame(mode):
     assert q.get(timeout=5) is True
 
 
+def _gather_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import rustraytrace_b200 as R
+    from rustraytrace_b200 import distributed
+    F = R._ffi
+    cam = R.make_camera(image_width=100, aspect_ratio=16 / 9, samples_per_pixel=4)   # 100 x 56: ragged edge tiles
+    full = R.shard_plan(cam, F.INT_BOOK2, F.SHARD_NONE, 0, 1, mask=True)
+    want = _frame(cam, 4, (0, 4), full["mask"])
+    plan = R.shard_plan(cam, F.INT_BOOK2, F.SHARD_TILE, rank, world, mask=True)
+    mine = distributed.pack_tiles_host(want * plan["mask"][..., None], rank, world)   # what the kernel's compact mode writes
+    assert mine.size == plan["n_super_tiles"] * 1024 * 4
+    sizes = [R.shard_plan(cam, F.INT_BOOK2, F.SHARD_TILE, r, world)["n_super_tiles"] * 4096 for r in range(world)]
+    pad = torch.zeros(max(sizes)); pad[:mine.size] = torch.from_numpy(mine)
+    got = [torch.zeros(max(sizes)) for _ in range(world)] if rank == 0 else None
+    dist.gather(pad, got, dst=0)
+    if rank == 0:
+        frame = R.tile_scatter_host(cam, [g.numpy()[:n] for g, n in zip(got, sizes)])
+        q.put(bool(np.array_equal(frame, want)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_gather_of_owned_tiles_rebuilds_the_frame(world):
+    """Tile sharding as the library exchanges it: every rank sends only its own packed super tiles,
+    rank 0 scatters them (rrt_tile_scatter_host = the host mirror of tile_scatter_kernel)."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_gather_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    assert q.get(timeout=5) is True
+
+
 def test_combine_host_is_the_same_sum():
     from rustraytrace_b200 import distributed
     a = np.ones((2, 3, 4), dtype=np.float32); b = 2 * a

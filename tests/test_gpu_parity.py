@@ -60,7 +60,7 @@ def test_probe_f32_kernel_close(ctx, book, scene_no):
     # measured at full size (tests/golden/probe_f32.json, gated there at twice the measurement): at most
     # 3e-5 of the ids differ (silhouettes), t within 5e-3 on the r = 1000 ground sphere near the horizon and
     # within 3e-5 at the 99th percentile; this is the 640-px smoke version of that test
-    assert (ids != oids).mean() < 1e-4
+    assert (ids != oids).mean() < 5e-4      # silhouette pixels: their share grows as the frame shrinks (C5 at 3840 px: 3e-5)
     same = (ids == oids) & (oids >= 0)
     rel = np.abs(t[same] - ot[same]) / ot[same]
     assert np.median(rel) < 1e-6 and np.quantile(rel, 0.99) < 6e-5 and rel.max() < 1e-2
