@@ -14,10 +14,13 @@ the gamma resolve to RGB8, through the C ABI of librrt.so (include/rrt.h).
          src/cuda/mod.rs:342-441) with HOST buffers: host scene description in, flatten + BVH build
          + H2D + render + D2H of the RGBA-sum frame into pinned host memory, wall clock.
 
-N = 1 renders BASELINE.json configs[1] (C2).  N > 1 is weak scaling on the sample axis: the frame
-keeps its size, samples-per-pixel become 500*N, rank r renders samples [500r, 500(r+1)) of every
-pixel (RRT_SHARD_SAMPLE) and the RGBA-sum frames are SUM-reduced to rank 0 over NCCL inside the
-timed region (C5 shards by interleaved tiles instead).
+N = 1 renders BASELINE.json configs[1] (C2) as the headline and, after it, every other config at its
+full size and spp (`configs`: C1, C3a, C3b, C3c, C4, C5).  N > 1 is STRONG scaling: the same C2 frame
+(1200x675, 500 spp) split into N sample ranges, rendered and exchanged inside librrt.so
+(rrt_render_collective: ncclReduce of the RGBA-sum frames to rank 0, inside the timed region), plus
+`strong_scaling`: the two configs north_star shards — C4 (800x800, 10 000 spp) by sample ranges and C5
+(3840x3840, 4096 spp) by interleaved tiles with a gather of owned tiles.  The N = 1 line carries C4 and
+C5 in `configs`, so efficiency at N is strong_scaling[key].value / (N x configs[key].value at N = 1).
 
 --impl reference times the CPU path (the ORACLE restatement of the reference's Rust renderer —
 the Rust itself cannot be built in this image) on all host threads, on a bounded row sample of the
@@ -43,7 +46,7 @@ SM_LANES = 128  # FP32 lanes per SM (4 SMSPs x 32)
 
 def workload_name(key, n_gpus):
     from rustraytrace_b200 import configs
-    return configs.DESCRIPTION[key] + (f", spp x{n_gpus} (weak scaling on the sample axis)" if n_gpus > 1 else "")
+    return configs.DESCRIPTION[key]
 
 
 def env_int(name, default):
@@ -140,14 +143,140 @@ def run_reference(args, rank, world):
     value = sum(vals) / len(vals)
     line = {"impl": "reference", "metric": METRIC, "value": round(value, 4), "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * sum(dts) / len(dts), 2),
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(args.config, args.gpus), "key": args.config,
-                       "note": "CPU restatement (oracle port) of the reference's Rust renderer; rustc/cargo absent"},
+                       "note": "CPU restatement (oracle port) of the reference's Rust renderer; rustc/cargo absent. "
+                               "The scene description it renders is built by librrt_host.so (host/books.cpp), the same "
+                               "builder the GPU arm uses; the render itself runs in oracle/liboracle.so only"},
             "cpu_baseline": {"value": round(value, 4), "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": round(value, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
     return 0
+
+
+def measure(ctx, key, mode, rank, world, steps, warmup, stream, flush, e2e_steps=0, spp_override=0, sampler=None):
+    """One config, strong scaling over `world` ranks: device-resident throughput (CUDA events on the
+    launching stream, L2 flushed between steps) and, when e2e_steps > 0, the host-buffer end-to-end call.
+    Collective: every rank calls it with the same arguments.  Returns a dict (complete on rank 0)."""
+    import torch
+    import torch.distributed as dist
+    import rustraytrace_b200 as R
+    from rustraytrace_b200 import configs
+    F = R._ffi
+    ov = {"samples_per_pixel": spp_override} if spp_override > 0 else {}
+    scene = configs.build(key, **ov)
+    W, H = scene.width, scene.height
+    gs = ctx.scene(scene.desc)
+    shard = {"sample": F.SHARD_SAMPLE, "tile": F.SHARD_TILE}[mode]
+    accum = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda") if rank == 0 else None
+    rgb8 = torch.zeros((H, W, 3), dtype=torch.uint8, device="cuda") if rank == 0 else None
+
+    def step():
+        if world > 1:
+            ctx.render_collective(gs, scene.camera, scene.integrator, seed=1, shard_mode=shard,
+                                  accum_ptr=accum.data_ptr() if rank == 0 else None)
+        else:
+            ctx.render_device(gs, scene.camera, scene.integrator, accum.data_ptr(), seed=1)
+        st = ctx.stats()
+        if rank == 0:
+            ctx.resolve_device(accum.data_ptr(), W, H, st["spp_effective"], rgb8.data_ptr())
+        return st
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(warmup):
+        flush.fill_(1)
+        st = step()
+    barrier()
+    if sampler:
+        sampler.start()
+        time.sleep(0.3)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    kernel_ms = exchange_ms = my_paths = 0.0
+    launches = 0
+    barrier()
+    t_wall0 = time.perf_counter()
+    for a, b in ev:
+        flush.fill_(1)          # L2 flush between timed iterations (outside the event pair)
+        a.record(stream)
+        st = step()
+        b.record(stream)
+        kernel_ms += st["kernel_ms"]; exchange_ms += st["exchange_ms"]
+        launches += st["kernel_launches"] + (1 if rank == 0 else 0)   # render (+ tile scatter) + resolve on rank 0
+        my_paths += st["paths"]
+    barrier()
+    wall_s = time.perf_counter() - t_wall0
+    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+    clocks = sampler.stop() if sampler else None
+    tot = torch.tensor([dev_ms, kernel_ms], dtype=torch.float64, device="cuda")
+    paths_t = torch.tensor([my_paths], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tot, op=dist.ReduceOp.MAX)
+        dist.all_reduce(paths_t, op=dist.ReduceOp.SUM)
+    dev_ms_max, kernel_ms_max = tot.tolist()
+    total_paths = paths_t.item()
+    out = {"key": key, "workload": configs.DESCRIPTION[key], "width": W, "height": H, "spp": st["spp_effective"],
+           "max_depth": scene.camera.max_depth, "steps": steps, "warmup": warmup,
+           "value": round(total_paths / (dev_ms_max * 1e-3) / 1e6, 2), "unit": UNIT,
+           "ms_per_step": round(dev_ms_max / steps, 3), "kernel_ms": round(kernel_ms_max / steps, 3),
+           "exchange_ms_rank0": round(exchange_ms / steps, 3), "kernel_share_of_step": round(kernel_ms_max / dev_ms_max, 4),
+           "paths_per_step": total_paths / steps, "my_paths_per_step": my_paths / steps, "gpu_launches": launches, "wall_s": round(wall_s, 3),
+           "prims": st["n_prims"], "bvh_nodes": st["n_bvh_nodes"], "sm_count": st["sm_count"], "kernel_features": st["kernel_features"],
+           "sharding": "none" if world == 1 else (("sample ranges + ncclReduce(SUM) to rank 0" if mode == "sample" else
+                                                   "interleaved 32x32 tiles + gather of owned tiles to rank 0") + f", {world} ranks, inside librrt.so"),
+           "clocks": clocks, "integrator": scene.integrator}
+    f_path = configs.F_PATH.get(key)
+    if f_path:
+        peaks, _ = measured_peaks()
+        peak = st["sm_count"] * SM_LANES * 2 * float(peaks.get("sm_max_mhz", 1965.0)) * 1e6 / 1e12
+        out["flops_per_path"] = f_path
+        # per GPU: this rank's paths through this rank's kernel
+        out["roofline_frac"] = round((my_paths / steps) * f_path / (kernel_ms / steps * 1e-3) / 1e12 / peak, 4) if kernel_ms > 0 else None
+    if rank == 0:
+        a = accum.double().sum(dim=(0, 1)).tolist()
+        out["frame_mean_radiance"] = [round(a[i] / a[3], 5) for i in range(3)]
+        assert abs(a[3] - float(W) * H * st["spp_effective"]) < 0.5, "frame is missing samples"
+
+    # ---- e2e: the host-buffer call, every rank its share, exchange inside the library, D2H on rank 0
+    if e2e_steps > 0:
+        host = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True) if rank == 0 else None
+        host_np = host.numpy() if rank == 0 else None
+        h2d = d2h = 0
+        e2e_s = 0.0
+        for i in range(1 + e2e_steps):
+            barrier()
+            t0 = time.perf_counter()
+            if world == 1:
+                ctx.render_frame(scene.desc, scene.camera, scene.integrator, seed=1, out=host_np)
+                s2 = ctx.stats()
+                h2d, d2h = s2["h2d_bytes"], s2["d2h_bytes"]
+            else:
+                g2 = ctx.scene(scene.desc)          # flatten + BVH build + H2D on every rank
+                h2d = ctx.stats()["h2d_bytes"]
+                ctx.render_collective(g2, scene.camera, scene.integrator, seed=1, shard_mode=shard, out=host_np)
+                d2h = ctx.stats()["d2h_bytes"]
+                g2.close()
+            barrier()
+            if i > 0:
+                e2e_s += time.perf_counter() - t0
+        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        out["e2e"] = {"value": round(total_paths / steps * e2e_steps / t.item() / 1e6, 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+                      "d2h_bytes_per_step": int(d2h), "steps": e2e_steps, "ms_per_step": round(1e3 * t.item() / e2e_steps, 3),
+                      "call": "rrt_render_frame (host scene description in, pinned RGBA-sum frame out)" if world == 1 else
+                              "rrt_scene_create + rrt_render_collective (share + NCCL exchange in librrt.so, pinned frame out on rank 0), every rank"}
+    gs.close()
+    return out
+
+
+# the other BASELINE.json configs in the driver's line: (key, timed steps, warm-up steps); every one at its full size and spp
+OTHER_CONFIGS = [("C1", 3, 2), ("C3a", 3, 1), ("C3b", 3, 1), ("C3c", 3, 1), ("C4", 2, 1), ("C5", 2, 1)]
+STRONG_CONFIGS = [("C4", 2, 1), ("C5", 2, 1)]   # the configs north_star shards: sample ranges / tiles
 
 
 def main():
@@ -161,6 +290,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the e2e leg (profiling runs)")
+    ap.add_argument("--no-configs", action="store_true", help="skip the other configs (profiling runs)")
     args = ap.parse_args()
     rank, local_rank, world = env_int("RANK", 0), env_int("LOCAL_RANK", 0), env_int("WORLD_SIZE", 1)
     if args.impl != "reference" and args.gpus != world:
@@ -169,7 +299,6 @@ def main():
         return run_reference(args, rank, world)
     args.warmup = max(3, args.warmup) if args.spp == 0 else args.warmup
 
-    import numpy as np
     import torch
     import torch.distributed as dist
     import rustraytrace_b200 as R
@@ -183,113 +312,33 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     n_gpus = world
 
-    book, scene_no, ov, mode = configs.CONFIGS[args.config]
-    base_spp = args.spp if args.spp > 0 else ov["samples_per_pixel"]
-    # weak scaling on the sample axis (tile mode: on the frame's spp as well, shares are tiles)
-    spp = base_spp * n_gpus
-    scene = configs.build(args.config, samples_per_pixel=spp)
-    W, H = scene.width, scene.height
-
     ctx = R.Context(local_rank)
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)
     ctx.set_stream(stream.cuda_stream)
-    gs = ctx.scene(scene.desc)
-    accum = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
-    rgb8 = torch.zeros((H, W, 3), dtype=torch.uint8, device="cuda")
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
-
-    def step():
-        distributed.render_sharded(ctx, gs, scene.camera, scene.integrator, accum, seed=1, mode=mode, rank=rank, world=n_gpus)
-        st = ctx.stats()
-        if rank == 0:
-            ctx.resolve_device(accum.data_ptr(), W, H, st["spp_effective"], rgb8.data_ptr())
-        return st
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(args.warmup):
-        flush.fill_(1)
-        st = step()
-    barrier()
-
-    sampler = ClockSampler(local_rank) if rank == 0 else None
-    if sampler:
-        sampler.start()
-        time.sleep(0.3)
-    # ---- device-resident timed region: K steps, each bracketed by events on the launching stream
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    kernel_ms, launches, my_paths = 0.0, 0, 0.0
-    barrier()
-    t_wall0 = time.perf_counter()
-    for a, b in ev:
-        flush.fill_(1)          # L2 flush between timed iterations (outside the event pair)
-        a.record(stream)
-        st = step()
-        b.record(stream)
-        kernel_ms += st["kernel_ms"]
-        launches += 1 + (1 if rank == 0 else 0)  # render kernel (+ resolve kernel on rank 0)
-        my_paths += st["paths"]
-    barrier()
-    wall_s = time.perf_counter() - t_wall0
-    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
-    clocks = sampler.stop() if sampler else None
-
-    tot = torch.tensor([dev_ms, kernel_ms], dtype=torch.float64, device="cuda")
-    paths_t = torch.tensor([my_paths], dtype=torch.float64, device="cuda")
     if world > 1:
-        dist.all_reduce(tot, op=dist.ReduceOp.MAX)
-        dist.all_reduce(paths_t, op=dist.ReduceOp.SUM)
-    dev_ms_max, kernel_ms_max = tot.tolist()
-    total_paths = paths_t.item()
-    value = total_paths / (dev_ms_max * 1e-3) / 1e6
-    frame_mean = None
-    if rank == 0:
-        a = accum.double().sum(dim=(0, 1)).tolist()
-        frame_mean = [round(a[i] / a[3], 5) for i in range(3)]
-        assert abs(a[3] - float(W) * H * st["spp_effective"]) < 0.5, "frame is missing samples"
+        distributed.init_comm_from_torch(ctx)   # torch carries the NCCL id; the exchange itself is librrt's
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+    diag = args.spp > 0 or args.no_configs
 
-    # ---- e2e: the one-shot host-buffer call, every rank its share, reduce on device, D2H on rank 0
-    e2e = None
-    if not args.no_e2e:
-        host = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True)
-        host_np = host.numpy()
-        n_e2e = max(1, min(args.steps, 3))
-        h2d = d2h = 0
-        e2e_s = 0.0
-        for i in range(1 + n_e2e):
-            barrier()
-            t0 = time.perf_counter()
-            if world == 1:
-                ctx.render_frame(scene.desc, scene.camera, scene.integrator, seed=1, out=host_np)
-                s2 = ctx.stats()
-                h2d, d2h = s2["h2d_bytes"], s2["d2h_bytes"]
-            else:
-                g2 = ctx.scene(scene.desc)          # flatten + BVH build + H2D
-                h2d = ctx.stats()["h2d_bytes"]
-                distributed.render_sharded(ctx, g2, scene.camera, scene.integrator, accum, seed=1, mode=mode, rank=rank, world=n_gpus)
-                if rank == 0:
-                    host.copy_(accum, non_blocking=True)
-                    d2h = host.numel() * 4
-                g2.close()
-            barrier()
-            if i > 0:
-                e2e_s += time.perf_counter() - t0
-        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_paths = total_paths / args.steps * n_e2e
-        e2e = {"value": round(e2e_paths / t.item() / 1e6, 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
-               "d2h_bytes_per_step": int(d2h), "steps": n_e2e, "ms_per_step": round(1e3 * t.item() / n_e2e, 3),
-               "call": "rrt_render_frame (host scene description in, pinned RGBA-sum frame out)" if world == 1 else
-                       "rrt_scene_create + rrt_render_device + NCCL reduce + D2H on rank 0"}
+    mode = configs.CONFIGS[args.config][3]
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    head = measure(ctx, args.config, mode, rank, world, args.steps, args.warmup, stream, flush,
+                   e2e_steps=0 if args.no_e2e else args.steps, spp_override=args.spp, sampler=sampler)
+    others, strong = {}, {}
+    if not diag:
+        if n_gpus == 1:
+            for key, k, w in OTHER_CONFIGS:
+                if key != args.config:
+                    others[key] = measure(ctx, key, configs.CONFIGS[key][3], rank, world, k, w, stream, flush, e2e_steps=1 if key in ("C4", "C5") else 0)
+        else:
+            for key, k, w in STRONG_CONFIGS:
+                strong[key] = measure(ctx, key, configs.CONFIGS[key][3], rank, world, k, w, stream, flush, e2e_steps=1)
 
     if rank == 0:
         peaks, peak_src = measured_peaks()
-        sm_count = st["sm_count"]
+        sm_count = head["sm_count"]
+        W, H = head["width"], head["height"]
         f_path = configs.F_PATH.get(args.config)
         cpu = None
         if n_gpus == 1 and not args.no_cpu:
@@ -297,13 +346,13 @@ def main():
             cpu = {"value": round(v, 4), "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port", "sample": sample,
                    "flops_per_path_live": round(f_live, 1)}
         ref_cuda = None
-        if n_gpus == 1 and not args.no_cpu and scene.integrator == F.INT_BOOK1:
+        if n_gpus == 1 and not args.no_cpu and head["integrator"] == F.INT_BOOK1:
             # the reference's existing src/cuda path, same scene, same box, its own launch shape
             # (oracle/_ref/libref_cuda.so, tests/ref_cuda_ffi.py); it supports book-1 scenes only
             try:
                 import ref_cuda_ffi as RC
                 if RC.available():
-                    rs = configs.build(args.config, samples_per_pixel=min(128, st["spp_effective"]))
+                    rs = configs.build(args.config, samples_per_pixel=min(128, head["spp"]))
                     RC.render(configs.build(args.config, samples_per_pixel=4))   # warm-up
                     racc, rms, rpasses = RC.render(rs)
                     rpaths = float(W) * H * rs.camera.samples_per_pixel
@@ -316,10 +365,9 @@ def main():
                 ref_cuda = {"unavailable": repr(e)}
         sm_max = float(peaks.get("sm_max_mhz", 1965.0))
         peak_tf = sm_count * SM_LANES * 2 * sm_max * 1e6 / 1e12
-        # dominant kernel = render_kernel: algorithmic flops per launch / its mean launch duration
-        paths_per_launch = my_paths / args.steps
-        k_ms = kernel_ms / args.steps
-        achieved = (paths_per_launch * f_path / (k_ms * 1e-3) / 1e12) if f_path else None
+        # dominant kernel = render_kernel: algorithmic flops per launch / its mean launch duration (rank 0's launch)
+        k_ms = head["kernel_ms"]
+        achieved = (head["my_paths_per_step"] * f_path / (k_ms * 1e-3) / 1e12) if f_path else None
         traffic, traffic_src = None, None
         import glob
         caps = sorted(glob.glob(os.path.join(ROOT, "profiles", "ncu_r*_render_kernel_c2_spp64.csv")))
@@ -331,29 +379,40 @@ def main():
                 if k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
                     tot += float(v) * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u, 1)
             traffic, traffic_src = int(tot), "profiles/" + os.path.basename(ncu_csv) + " (64-spp launch; DRAM traffic is the frame, independent of spp)"
+        clocks = head["clocks"]
         roof = {"bound": "fp32", "achieved": round(achieved, 3) if achieved else None, "peak": round(peak_tf, 2),
                 "unit": "TFLOP/s", "frac": round(achieved / peak_tf, 4) if achieved else None, "traffic": traffic, "traffic_source": traffic_src,
                 "algorithmic_dram_bytes": W * H * 16,
                 "kernel": "render_kernel", "kernel_ms": round(k_ms, 3), "flops_per_path": f_path,
                 "peak_source": f"{sm_count} SMs x 128 lanes x 2 x sm_max_mhz {sm_max:.0f} ({peak_src} MEASURED_PEAKS.json); "
                                "path tracing is FP32-pipe/latency bound, neither HBM nor tensor",
-                "kernel_share_of_step": round(kernel_ms_max / dev_ms_max, 4)}
+                "kernel_share_of_step": head["kernel_share_of_step"]}
         if clocks and clocks.get("sm_mhz") and achieved:
             roof["frac_at_observed_clock"] = round(achieved / (sm_count * SM_LANES * 2 * clocks["sm_mhz"] * 1e6 / 1e12), 4)
-        line = {"metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": round(dev_ms_max / args.steps, 3), "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": workload_name(args.config, n_gpus),
-                           "key": args.config, "width": W, "height": H, "spp": st["spp_effective"],
-                           "max_depth": scene.camera.max_depth, "scene_seed": hex(configs.SCENE_SEED),
-                           "sharding": "none" if n_gpus == 1 else ("sample ranges" if mode == "sample" else "interleaved 32x32 tiles") + f" over {n_gpus} ranks + NCCL sum-reduce to rank 0",
-                           "l2": "flushed between steps (256 MiB fill)", "prims": st["n_prims"], "bvh_nodes": st["n_bvh_nodes"]},
-                "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu, "ref_cuda_kernel": ref_cuda, "clocks": clocks,
-                "wall_s": round(wall_s, 3), "frame_mean_radiance": frame_mean}
+
+        def brief(d):
+            keep = ("workload", "width", "height", "spp", "max_depth", "steps", "warmup", "value", "unit", "ms_per_step", "kernel_ms",
+                    "exchange_ms_rank0", "flops_per_path", "roofline_frac", "sharding", "frame_mean_radiance", "e2e", "kernel_features")
+            return {k: d[k] for k in keep if k in d}
+
+        line = {"metric": METRIC, "value": head["value"], "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": head["ms_per_step"], "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": head["workload"] + (f", one frame over {n_gpus} GPUs (strong scaling)" if n_gpus > 1 else ""),
+                           "key": args.config, "width": W, "height": H, "spp": head["spp"],
+                           "max_depth": head["max_depth"], "scene_seed": hex(configs.SCENE_SEED),
+                           "sharding": head["sharding"],
+                           "l2": "flushed between steps (256 MiB fill)", "prims": head["prims"], "bvh_nodes": head["bvh_nodes"]},
+                "e2e": head.get("e2e"), "gpu_launches": head["gpu_launches"], "roofline": roof, "cpu_baseline": cpu, "ref_cuda_kernel": ref_cuda,
+                "clocks": clocks, "exchange_ms_rank0": head["exchange_ms_rank0"],
+                "wall_s": head["wall_s"], "frame_mean_radiance": head.get("frame_mean_radiance")}
+        if others:
+            line["configs"] = {k: brief(v) for k, v in others.items()}
+        if strong:
+            line["strong_scaling"] = {k: brief(v) for k, v in strong.items()}
         if args.spp > 0:
             line["config"]["diagnostic_spp_override"] = args.spp
         print(json.dumps(line), flush=True)
-    gs.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -18,6 +18,7 @@
 #include <nccl.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -35,6 +36,10 @@ using namespace rrt;
 namespace {
 
 ncclComm_t comm_of(const rrt_ctx* c) { return reinterpret_cast<ncclComm_t>(c->comm); }
+
+// NCCL prints its version banner (NCCL_DEBUG=VERSION/INFO) on stdout, which is where the CLI writes the
+// PPM (render_io.rs:3-30 prints to stdout): send NCCL's text to stderr unless the user chose a file.
+void nccl_text_to_stderr() { setenv("NCCL_DEBUG_FILE", "/dev/stderr", 0); }
 
 int resolve_mode(const rrt_render_params* p) { return p->shard_mode == RRT_SHARD_TILE ? RRT_SHARD_TILE : RRT_SHARD_SAMPLE; }
 
@@ -114,6 +119,7 @@ int scatter_enqueue(rrt_ctx* root, int world, const FramePlan& f, float* frame_r
 int rrt::multi_comm_init_all(rrt_ctx* g, const int* devices) {
   const int n = (int)g->members.size();
   std::vector<ncclComm_t> comms(n);
+  nccl_text_to_stderr();
   NK(ncclCommInitAll(comms.data(), n, devices), "ncclCommInitAll");
   for (int i = 0; i < n; ++i) {
     g->members[i]->comm = comms[i];
@@ -213,6 +219,7 @@ int rrt_comm_unique_id(uint8_t* id128) {
   if (!id128) return rrt::fail(RRT_ERR_INVALID, "rrt_comm_unique_id: id128 is null");
   static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
   ncclUniqueId id;
+  nccl_text_to_stderr();
   NK(ncclGetUniqueId(&id), "ncclGetUniqueId");
   std::memcpy(id128, &id, sizeof id);
   return RRT_OK;
@@ -224,6 +231,7 @@ int rrt_comm_init(rrt_ctx* c, const uint8_t* id128, int rank, int world) {
   if (world < 1 || world > RRT_MAX_WORLD || rank < 0 || rank >= world) return rrt::fail(RRT_ERR_INVALID, "rrt_comm_init: rank/world out of range");
   CK(cudaSetDevice(c->device), "cudaSetDevice");
   comm_release(c);
+  nccl_text_to_stderr();
   ncclUniqueId id;
   std::memcpy(&id, id128, sizeof id);
   ncclComm_t comm;

@@ -24,7 +24,9 @@ static void usage() {
   std::fprintf(stderr, "example: rrt the_next_week 3\n");
   std::fprintf(stderr, "render flags (RenderOverrides, src/config.rs:1-14): --width N --spp N --depth N --aspect R --vfov D\n"
                        "  --lookfrom x,y,z --lookat x,y,z --vup x,y,z --defocus-angle D --focus-dist F --background r,g,b\n"
-                       "  --no-overrides (scene defaults)  --seed N (scene RNG)  --sample-seed N  --device N  -o FILE  --probe\n");
+                       "  --no-overrides (scene defaults)  --seed N (scene RNG)  --sample-seed N  --device N  -o FILE  --probe\n"
+                       "  --devices 0,1,..  render on several GPUs of this box (sample ranges + NCCL reduce; --shard tile: interleaved\n"
+                       "                    32x32 tiles + gather)\n");
 }
 
 int main(int argc, char** argv) {
@@ -34,6 +36,8 @@ int main(int argc, char** argv) {
   rrth_overrides_shipped(&ov);
   uint64_t scene_seed = 0x5EED1234ull, sample_seed = 1;
   int device = 0;
+  std::vector<int> devices;   // --devices: a multi-GPU group (rrt_init_multi)
+  int shard_mode = RRT_SHARD_NONE;
   const char* out_path = nullptr;
   bool probe = false;
   for (int i = 1; i < argc; ++i) {
@@ -60,6 +64,25 @@ int main(int argc, char** argv) {
     if (a == "--seed") { scene_seed = std::strtoull(next("--seed"), nullptr, 0); continue; }
     if (a == "--sample-seed") { sample_seed = std::strtoull(next("--sample-seed"), nullptr, 0); continue; }
     if (a == "--device") { device = std::atoi(next("--device")); continue; }
+    if (a == "--devices") {
+      const char* v = next("--devices");
+      devices.clear();
+      for (const char* q = v; *q;) {
+        char* end = nullptr;
+        long d = std::strtol(q, &end, 10);
+        if (end == q) { std::fprintf(stderr, "--devices expects a comma-separated list of device indices\n"); return 2; }
+        devices.push_back((int)d);
+        q = *end == ',' ? end + 1 : end;
+      }
+      continue;
+    }
+    if (a == "--shard") {
+      std::string v = next("--shard");
+      if (v == "tile") shard_mode = RRT_SHARD_TILE;
+      else if (v == "sample") shard_mode = RRT_SHARD_SAMPLE;
+      else { std::fprintf(stderr, "--shard expects tile or sample\n"); return 2; }
+      continue;
+    }
     if (a == "-o") { out_path = next("-o"); continue; }
     if (a == "--probe") { probe = true; continue; }
     if (a == "-h" || a == "--help") { usage(); return 0; }
@@ -90,7 +113,8 @@ int main(int argc, char** argv) {
   const rrt_camera* cam = rrth_scene_camera(hs);
   const int W = cam->image_width, H = rrt_image_height(cam);
   rrt_ctx* ctx = nullptr;
-  if (rrt_init(device, &ctx) != RRT_OK) {
+  const int init_rc = devices.empty() ? rrt_init(device, &ctx) : rrt_init_multi(devices.data(), (int)devices.size(), &ctx);
+  if (init_rc != RRT_OK) {
     std::fprintf(stderr, "CUDA render failed: %s\n", rrt_last_error());  // main.rs:62-65 wording
     rrth_scene_free(hs);
     return 1;
@@ -118,16 +142,18 @@ int main(int argc, char** argv) {
     rrt_render_params p;
     std::memset(&p, 0, sizeof p);
     p.integrator = rrth_scene_integrator(hs);
-    p.shard_mode = RRT_SHARD_NONE; p.rank = 0; p.world = 1; p.seed = sample_seed;
-    std::fprintf(stderr, "Rendering %dx%d, %d spp, depth %d on device %d ...\n", W, H, cam->samples_per_pixel, cam->max_depth, device);
+    p.shard_mode = devices.empty() ? RRT_SHARD_NONE : shard_mode; p.rank = 0; p.world = 1; p.seed = sample_seed;
+    if (devices.empty()) std::fprintf(stderr, "Rendering %dx%d, %d spp, depth %d on device %d ...\n", W, H, cam->samples_per_pixel, cam->max_depth, device);
+    else std::fprintf(stderr, "Rendering %dx%d, %d spp, depth %d on %d devices (%s) ...\n", W, H, cam->samples_per_pixel, cam->max_depth,
+                      (int)devices.size(), shard_mode == RRT_SHARD_TILE ? "interleaved tiles" : "sample ranges");
     if (rrt_render_frame(ctx, rrth_scene_desc(hs), cam, &p, accum.data()) != RRT_OK) {
       std::fprintf(stderr, "CUDA render failed: %s\n", rrt_last_error());
       rc = 1;
     } else {
       rrt_stats st;
       rrt_get_stats(ctx, &st);
-      std::fprintf(stderr, "Done: %.0f paths in %.1f ms (%.1f Mpaths/s), %d prims, %d BVH nodes\n", st.paths, st.kernel_ms,
-                   st.paths / st.kernel_ms / 1e3, st.n_prims, st.n_bvh_nodes);
+      std::fprintf(stderr, "Done: %.0f paths in %.1f ms (%.1f Mpaths/s), %d prims, %d BVH nodes, %d GPU(s), exchange %.2f ms\n", st.paths,
+                   st.kernel_ms, st.paths / st.kernel_ms / 1e3, st.n_prims, st.n_bvh_nodes, st.n_devices, st.exchange_ms);
       if (rrth_write_ppm_from_accum(out_path, W, H, accum.data(), (uint32_t)st.spp_effective) != 0) {
         std::fprintf(stderr, "could not write the image: %s\n", rrth_last_error());
         rc = 1;

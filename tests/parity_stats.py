@@ -5,9 +5,12 @@ hypothesis that both sample the same per-pixel distribution (so one variance ser
     se^2 = var (1/n_img + 1/n_ref)
 Pixels are split in two classes:
   * flat pixels — relative standard error below 1e-4 (a constant background, the inside of a
-    uniformly lit object): there is no noise to normalise by, they must simply agree to f32 summation
-    precision, reported as flat_max_rel (4 096 f32 additions of the same value carry a coherent
-    rounding error of a few 1e-6, which a z score would blow up into a "bias");
+    uniformly lit object): there is no measured noise to normalise by (4 096 f32 additions of the same
+    value carry a coherent rounding error of a few 1e-6, which a z score would blow up into a "bias"),
+    so they are compared directly: flat_max_rel = the largest |difference| as a fraction of the frame's
+    mean radiance.  It is not zero — a pixel looks flat when none of the reference's samples met the
+    object whose rim crosses 1/5000 of it, and the other render's one sample that did moves the pixel by
+    ~1e-3 — but a wrong background or a shifted flat region is 10 to 1000 times that;
   * noisy pixels: per pixel and channel the fraction of |z| > 4 (outliers: a feature one side renders
     and the other does not), and per 4x4-pixel block the mean and rms of z.  Bias is judged on blocks,
     not on pixels: a path-traced pixel is a skewed distribution (rare bright paths), its sample mean
@@ -24,7 +27,7 @@ def z_stats(img, n_img, ref, var, n_ref, block=4):
     finite = np.isfinite(img) & np.isfinite(ref)
     noisy = finite & (se2 > (1e-4 * np.abs(ref)) ** 2)
     flat = finite & ~noisy
-    flat_rel = np.abs(img[flat] - ref[flat]) / np.maximum(np.abs(ref[flat]), 1e-3)
+    flat_rel = np.abs(img[flat] - ref[flat]) / float(np.mean(np.abs(ref[finite])))
     z = (img[noisy] - ref[noisy]) / np.sqrt(se2[noisy])
     H, W = img.shape[0] // block * block, img.shape[1] // block * block
     sh = (H // block, block, W // block, block, img.shape[2])

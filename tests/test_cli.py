@@ -50,3 +50,20 @@ def test_cli_book_aliases_probe_and_errors(tmp_path):
     assert bad.returncode == 1 and "books: in_one_weekend, the_next_week, the_rest_of_your_life" in bad.stderr
     bad = subprocess.run([RRT, "--backend", "vulkan", "weekend"], capture_output=True, text=True, timeout=60)
     assert bad.returncode == 2
+
+
+@pytest.mark.parametrize("devices,shard", [("0", "sample"), ("0", "tile"), ("0,1", "sample"), ("0,1", "tile")])
+def test_cli_devices_flag_renders_on_a_group(devices, shard):
+    """rrt --devices: the multi-GPU group of rrt_init_multi from the command line, no Python in the path."""
+    import torch
+    if len(devices.split(",")) > torch.cuda.device_count():
+        pytest.skip("needs two GPUs")
+    args = ["the_next_week", "2", "--width", "100", "--spp", "32", "--depth", "8", "--sample-seed", "3"]
+    one = subprocess.run([RRT] + args, capture_output=True, text=True, timeout=120)
+    many = subprocess.run([RRT] + args + ["--devices", devices, "--shard", shard], capture_output=True, text=True, timeout=180)
+    assert one.returncode == 0 and many.returncode == 0, many.stderr
+    assert f"{len(devices.split(','))} GPU(s)" in many.stderr
+    a, b = read_p3(one.stdout), read_p3(many.stdout)
+    assert a.shape == b.shape and np.abs(a - b).max() <= 1 and (a != b).mean() < 0.01
+    bad = subprocess.run([RRT, "weekend", "--devices", "0,0"], capture_output=True, text=True, timeout=60)
+    assert bad.returncode == 1 and "listed twice" in bad.stderr
