@@ -1,5 +1,5 @@
-// UNBUILT here: this image has no rustc/cargo.  Kept in sync with include/rrt.h by
-// tests/test_abi.py::test_rust_binding_declares_every_entry_point.  See INTEGRATION.md.
+// UNBUILT here: this image has no rustc/cargo (INTEGRATION.md §0).  Kept in sync with include/rrt.h by
+// tests/test_abi.py::test_rust_binding_declares_every_entry_point (names, field order, field types).
 // `mod rrt_ffi;` in the reference's src/main.rs; replaces src/cuda/mod.rs and src/gpu/mod.rs.
 use std::os::raw::{c_char, c_int, c_void};
 

@@ -71,7 +71,7 @@ int rrt::scene_upload(rrt_ctx* c, const FlatScene& F, rrt_scene** out) {
   int rc = RRT_OK;
   if ((rc = upload(sc, F.prims, &D.prims)) || (rc = upload(sc, F.prims64, &D.prims64)) ||
       (rc = upload(sc, F.nodes, &D.nodes)) || (rc = upload(sc, F.bprims, &D.bprims)) ||
-      (rc = upload(sc, F.boxes, &D.boxes)) || (rc = upload(sc, F.qpairs, &D.qpairs)) ||
+      (rc = upload(sc, F.boxes, &D.boxes)) || (rc = upload(sc, F.qpairs, &D.qpairs)) || (rc = upload(sc, F.nodes4, &D.nodes4)) ||
       (rc = upload(sc, F.materials, &D.materials)) || (rc = upload(sc, F.textures, &D.textures)) ||
       (rc = upload(sc, F.images, &D.images)) || (rc = upload(sc, F.texels, &texels)) ||
       (rc = upload(sc, F.perlins, &D.perlins)) || (rc = upload(sc, F.media, &D.media)) ||
@@ -169,7 +169,8 @@ int rrt::render_enqueue(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, 
   // +3.5 %, C5 +1-6 %).  Not for one- and two-primitive scenes (near-constant path cost; the shared
   // counters cost 9 % on C3b) nor for the Perlin instances, which sit at their register limit (C4 -4 %).
   const bool steal = sc->n_prims > 2 && !(variant->features & SF_NOISE) && !c->no_steal && !c->deterministic;
-  int bps = render_blocks_per_sm(variant, steal);
+  const int schedule = c->use_pool && variant->kernel_pool && !c->deterministic ? RS_POOL : steal ? RS_STEAL : RS_OWN;
+  int bps = render_blocks_per_sm(variant, schedule);
   if (bps < 1) return fail(RRT_ERR_CUDA, "kernel launch failed: render kernel does not fit on an SM");
   const int grid = c->sm_count * bps;
   const long long resident_warps = (long long)grid * (RRT_BLOCK / 32);
@@ -195,7 +196,7 @@ int rrt::render_enqueue(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, 
   int launches = 0;
   CK(cudaEventRecord(c->ev[1], c->stream), "cudaEventRecord");
   if (W.n_tiles > 0 && n_samples > 0) {
-    CK(launch_render(variant, steal, A, grid, c->stream), "kernel launch failed");
+    CK(launch_render(variant, schedule, A, grid, c->stream), "kernel launch failed");
     launches = 1;
   }
   CK(cudaEventRecord(c->ev[2], c->stream), "cudaEventRecord");
@@ -253,6 +254,7 @@ static int init_device_ctx(int device, rrt_ctx** out) {
   c->force_full_kernel = kv && std::strcmp(kv, "full") == 0;
   c->no_steal = std::getenv("RRT_NO_STEAL") != nullptr;
   c->deterministic = std::getenv("RRT_DETERMINISTIC") != nullptr;
+  c->use_pool = std::getenv("RRT_POOL") != nullptr;
   e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);
   c->stream = c->own_stream;
   for (auto& ev : c->ev) if (e == cudaSuccess) e = cudaEventCreate(&ev);

@@ -34,6 +34,7 @@ struct rrt_ctx {
   rrt_stats stats;
   bool no_steal = false;              // RRT_NO_STEAL=1: lanes never take over neighbours' samples (debugging / A-B)
   bool deterministic = false;         // RRT_DETERMINISTIC=1: no stealing, one chunk per tile -> bit-reproducible frames
+  bool use_pool = false;              // RRT_POOL=1: the per-warp path-pool schedule where an instance has it (render_kernel_pool.cuh)
   bool force_full_kernel = false;     // RRT_KERNEL=full: always run the SF_ALL render kernel instance (include/rrt.h)
   std::vector<rrt_scene*> scenes;  // live scenes of this context (released by rrt_shutdown if the caller did not)
 

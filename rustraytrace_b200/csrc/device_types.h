@@ -155,6 +155,8 @@ struct DevScene {
   const float4* bprims;
   const float4* boxes;   // two float4 per box leaf
   const float4* qpairs;  // quad pair records of a brute-force root leaf, or null
+  const float4* nodes4;  // experiment (-DRRT_BVH4, profiles/README.md r02): the same tree collapsed to 4-wide nodes,
+                         //   8 float4 each: children 0,1 and 2,3 as two slab2 pair records, then the four refs; else null
   const double* prims64;
   const DevMaterial* materials;
   const DevTexture* textures;

@@ -828,11 +828,16 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
         continue;
       }
       int s = 0, q = 0;
-      for (int pass = 0; pass < 2; ++pass)
-        for (int k = n.first; k < n.first + n.count; ++k) {
-          const BakedPrim& p = items[B.order[k]];
-          if (p.kind == pass) { emit_prim32(p, out.prims); emit_prim64(p, out.prims64); (pass == 0 ? s : q)++; }
-        }
+      for (int pass = 0; pass < 2; ++pass) {
+        std::vector<int> run;
+        for (int k = n.first; k < n.first + n.count; ++k)
+          if (items[B.order[k]].kind == pass) run.push_back(B.order[k]);
+        // quads in the reference's visiting order: among quads a later one wins an exact-t tie (quad.rs:72
+        // `contains`), so a leaf that tests them in that order with `t <= closest` needs no tie lookup
+        // (quad_pairs_hit32 relies on it; quad_hit32's explicit rule agrees with it)
+        if (pass == 1) std::stable_sort(run.begin(), run.end(), [&](int a, int b) { return items[a].order < items[b].order; });
+        for (int i : run) { emit_prim32(items[i], out.prims); emit_prim64(items[i], out.prims64); (pass == 0 ? s : q)++; }
+      }
       leaf_ref[li] = make_leaf_ref(emitted, s, q);
       emitted += n.count;
     }
@@ -883,6 +888,46 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
     out.nodes.push_back(i4(ref0, ref1, 0, 0));
   }
   out.root_ref = 0;
+#ifdef RRT_BVH4
+  // Experiment (profiles/README.md, r02): the binary tree collapsed to 4-wide nodes — a node's children
+  // are its grandchildren (a leaf child stays one child) — so that a traversal step tests four boxes with
+  // two packed slab tests.  Same leaves, same boxes; breadth-first like the binary array.
+  {
+    std::vector<int> index4(B.nodes.size(), -1), bfs4;
+    auto kids = [&](int n, int* k) {   // up to four BNode indices
+      int c = 0;
+      const int ch[2] = {B.nodes[n].left, B.nodes[n].right};
+      for (int s = 0; s < 2; ++s) {
+        if (B.nodes[ch[s]].left < 0) k[c++] = ch[s];
+        else { k[c++] = B.nodes[ch[s]].left; k[c++] = B.nodes[ch[s]].right; }
+      }
+      return c;
+    };
+    std::queue<int> q; q.push(root);
+    while (!q.empty()) {
+      int n = q.front(); q.pop();
+      index4[n] = (int)bfs4.size(); bfs4.push_back(n);
+      int k[4]; int c = kids(n, k);
+      for (int i = 0; i < c; ++i) if (B.nodes[k[i]].left >= 0) q.push(k[i]);
+    }
+    for (int n : bfs4) {
+      int k[4]; const int c = kids(n, k);
+      float4 rec[8];
+      std::memset(rec, 0, sizeof rec);
+      int refs[4] = {0, 0, 0, 0};
+      for (int i = 0; i < 4; ++i) {
+        float cc[3] = {0, 0, 0}, hh[3] = {-1e30f, -1e30f, -1e30f};   // an empty slot: never hit
+        if (i < c) {
+          box32(B.nodes[k[i]].lo, B.nodes[k[i]].hi, cc, hh);
+          refs[i] = B.nodes[k[i]].left >= 0 ? index4[k[i]] : leaf_ref[k[i]];
+        }
+        node_set_child(rec + (i < 2 ? 0 : 3), i & 1, cc, hh);
+      }
+      rec[6] = i4(refs[0], refs[1], refs[2], refs[3]);
+      for (int i = 0; i < 8; ++i) out.nodes4.push_back(rec[i]);
+    }
+  }
+#endif
   return RRT_OK;
 }
 

@@ -16,6 +16,7 @@ struct FlatScene {
   std::vector<double> prims64;    // 16 per prim
   std::vector<float4> boxes;     // box leaves, two float4 each (device_types.h)
   std::vector<float4> nodes;      // 4 per inner node
+  std::vector<float4> nodes4;     // -DRRT_BVH4 experiment only: 8 per 4-wide node
   std::vector<float4> qpairs;     // root-leaf quads again, 6 float4 per pair (device_types.h)
   std::vector<float4> bprims;     // 4 per medium-boundary prim
   std::vector<DevMaterial> materials;

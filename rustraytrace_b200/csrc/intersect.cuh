@@ -15,6 +15,8 @@
 // the primitives' construction order: quad beats sphere; between quads the later wins; between
 // spheres the earlier wins.
 #pragma once
+#include <math_constants.h>
+
 #include "device_types.h"
 #include "vecmath.cuh"
 
@@ -204,8 +206,8 @@ __device__ __forceinline__ float2 mul2(float2 a, float2 b) {
 // The quads of a brute-force root leaf, two at a time (device_types.h quad pair record): Quad::hit
 // (quad.rs:64-91) for both as 16 packed FMAs and two reciprocals, every lane running the same
 // straight-line code; the reference's early-outs (parallel, t out of range, alpha / beta outside
-// [0, 1]) become one predicate per quad.  Quads are accepted in leaf order with t <= h.t, like the loop
-// of quad_hit32 calls this replaces, so the equal-t rules are unchanged.
+// [0, 1]) become one predicate per quad.  Quads are accepted in leaf order with t <= h.t; the leaf order
+// is the reference's visiting order, which makes that the reference's equal-t rule (see below).
 __device__ __forceinline__ void quad_pairs_hit32(const float4* __restrict__ prims, const float4* __restrict__ qp, int first, int nq,
                                                  const Ray32& r, float tmin, int skip, Hit32& h) {
   const float2 ox = bcast2(r.o.x), oy = bcast2(r.o.y), oz = bcast2(r.o.z);
@@ -221,11 +223,11 @@ __device__ __forceinline__ void quad_pairs_hit32(const float4* __restrict__ prim
     const float2 al = fma2(pz, make_float2(q3.x, q3.y), fma2(py, make_float2(q2.z, q2.w), fma2(px, make_float2(q2.x, q2.y), make_float2(q3.z, q3.w))));
     const float2 be = fma2(pz, make_float2(q5.x, q5.y), fma2(py, make_float2(q4.z, q4.w), fma2(px, make_float2(q4.x, q4.y), make_float2(q5.z, q5.w))));
     const int i0 = first + k, i1 = first + k + 1;
-    bool ok0 = (fabsf(denom.x) >= 1e-8f) & (t.x >= tmin) & (t.x <= h.t) & (al.x >= 0.0f) & (al.x <= 1.0f) & (be.x >= 0.0f) & (be.x <= 1.0f) & (i0 != skip);
-    if (ok0 && t.x == h.t) ok0 = tie_accept(prims, i0 | PRIM_QUAD_BIT, h.prim);
+    // exact-t ties: the leaf's quads are stored in the reference's visiting order (flatten.cpp) and come
+    // after its spheres, so `t <= closest` alone gives "a later quad replaces an equal-t hit" (quad.rs:72)
+    const bool ok0 = (fabsf(denom.x) >= 1e-8f) & (t.x >= tmin) & (t.x <= h.t) & (al.x >= 0.0f) & (al.x <= 1.0f) & (be.x >= 0.0f) & (be.x <= 1.0f) & (i0 != skip);
     if (ok0) { h.t = t.x; h.prim = i0 | PRIM_QUAD_BIT; }
-    bool ok1 = (fabsf(denom.y) >= 1e-8f) & (t.y >= tmin) & (t.y <= h.t) & (al.y >= 0.0f) & (al.y <= 1.0f) & (be.y >= 0.0f) & (be.y <= 1.0f) & (i1 != skip);
-    if (ok1 && t.y == h.t) ok1 = tie_accept(prims, i1 | PRIM_QUAD_BIT, h.prim);
+    const bool ok1 = (fabsf(denom.y) >= 1e-8f) & (t.y >= tmin) & (t.y <= h.t) & (al.y >= 0.0f) & (al.y <= 1.0f) & (be.y >= 0.0f) & (be.y <= 1.0f) & (i1 != skip);
     if (ok1) { h.t = t.y; h.prim = i1 | PRIM_QUAD_BIT; }
   }
 }
@@ -275,6 +277,52 @@ __device__ inline void world_hit32(const DevScene& S, const Ray32& r, float tmin
   asm("" : "+f"(oodx), "+f"(oody), "+f"(oodz));  // opaque: keep in registers, do not rematerialise in the loop
   int stack[RRT_STACK];
   int sp = 0;
+#ifdef RRT_BVH4
+  // Experiment: 4-wide nodes (flatten.cpp, -DRRT_BVH4): one step tests four boxes (two packed slab tests),
+  // orders the hits with a five-exchange network, descends into the nearest and pushes the rest.
+  const char* const nodes4_base = reinterpret_cast<const char*>(S.nodes4);
+  for (;;) {
+    bool done = false;
+    while (cur >= 0) {
+      const float4* g = reinterpret_cast<const float4*>(nodes4_base + (size_t)(unsigned)cur * 128u);
+      const float4 q0 = ldg4(g), q1 = ldg4(g + 1), q2 = ldg4(g + 2), q3 = ldg4(g + 3), q4 = ldg4(g + 4), q5 = ldg4(g + 5), q6 = ldg4(g + 6);
+      float n0, f0, n1, f1, n2, f2, n3, f3;
+      slab2(q0, q1, q2, idx, idy, idz, oodx, oody, oodz, tmin, h.t, n0, f0, n1, f1);
+      slab2(q3, q4, q5, idx, idy, idz, oodx, oody, oodz, tmin, h.t, n2, f2, n3, f3);
+      int r0 = __float_as_int(q6.x), r1 = __float_as_int(q6.y), r2 = __float_as_int(q6.z), r3 = __float_as_int(q6.w);
+      if (!(n0 <= f0 * 1.0000004f)) n0 = CUDART_INF_F;
+      if (!(n1 <= f1 * 1.0000004f)) n1 = CUDART_INF_F;
+      if (!(n2 <= f2 * 1.0000004f)) n2 = CUDART_INF_F;
+      if (!(n3 <= f3 * 1.0000004f)) n3 = CUDART_INF_F;
+#define RRT_CSWAP(a, b, ra, rb) { const bool s_ = b < a; const float ta_ = s_ ? b : a, tb_ = s_ ? a : b; const int ia_ = s_ ? rb : ra, ib_ = s_ ? ra : rb; a = ta_; b = tb_; ra = ia_; rb = ib_; }
+      RRT_CSWAP(n0, n1, r0, r1) RRT_CSWAP(n2, n3, r2, r3) RRT_CSWAP(n0, n2, r0, r2) RRT_CSWAP(n1, n3, r1, r3) RRT_CSWAP(n1, n2, r1, r2)
+#undef RRT_CSWAP
+      if (n0 < CUDART_INF_F) {   // nearest first; the others wait on the stack, farthest pushed first
+        if (n3 < CUDART_INF_F && sp < RRT_STACK) stack[sp++] = r3;
+        if (n2 < CUDART_INF_F && sp < RRT_STACK) stack[sp++] = r2;
+        if (n1 < CUDART_INF_F && sp < RRT_STACK) stack[sp++] = r1;
+        cur = r0;
+      } else {
+        if (sp == 0) { done = true; break; }
+        cur = stack[--sp];
+      }
+    }
+    if (done) break;
+    if (!(FEAT & SF_QUADS)) {
+      while (cur < 0) {
+        leaf1_hit32<FEAT>(S.prims, S.boxes, ~cur, r, V3f(idx, idy, idz), a, inv_a, tmin, skip, motion, h);
+        if (sp == 0) { done = true; break; }
+        cur = stack[--sp];
+      }
+      if (done) break;
+    } else if (cur < 0) {
+      leaf1_hit32<FEAT>(S.prims, S.boxes, ~cur, r, V3f(idx, idy, idz), a, inv_a, tmin, skip, motion, h);
+      if (sp == 0) break;
+      cur = stack[--sp];
+    }
+  }
+  return;
+#endif
   const char* const nodes_base = reinterpret_cast<const char*>(S.nodes);
   // while-while traversal (Aila & Laine 2009): every lane first descends through inner nodes until
   // it holds a leaf, then the warp reconverges and processes leaves together; the single mixed

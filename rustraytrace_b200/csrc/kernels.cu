@@ -130,14 +130,18 @@ const RenderVariant* select_render_variant(int integrator, int features, bool fo
   return &t[n - 1];  // SF_ALL is the last entry of every table
 }
 
-cudaError_t launch_render(const RenderVariant* v, bool steal, const RenderArgs& A, int grid, cudaStream_t st) {
-  void* args[] = {const_cast<RenderArgs*>(&A)};
-  return cudaLaunchKernel(reinterpret_cast<const void*>(steal ? v->kernel : v->kernel_own), dim3(grid), dim3(RRT_BLOCK), args, 0, st);
+static const void* render_entry(const RenderVariant* v, int schedule) {
+  return reinterpret_cast<const void*>(schedule == RS_POOL ? v->kernel_pool : schedule == RS_STEAL ? v->kernel : v->kernel_own);
 }
 
-int render_blocks_per_sm(const RenderVariant* v, bool steal) {
+cudaError_t launch_render(const RenderVariant* v, int schedule, const RenderArgs& A, int grid, cudaStream_t st) {
+  void* args[] = {const_cast<RenderArgs*>(&A)};
+  return cudaLaunchKernel(render_entry(v, schedule), dim3(grid), dim3(RRT_BLOCK), args, 0, st);
+}
+
+int render_blocks_per_sm(const RenderVariant* v, int schedule) {
   int n = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, reinterpret_cast<const void*>(steal ? v->kernel : v->kernel_own), RRT_BLOCK, 0) != cudaSuccess) {
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, render_entry(v, schedule), RRT_BLOCK, 0) != cudaSuccess) {
     cudaGetLastError();
     return 0;
   }

@@ -61,15 +61,17 @@ struct RenderVariant {
   int features;                 // SceneFeature bits the instance supports
   void (*kernel)(RenderArgs);      // __global__ entry, lanes take over neighbours' samples (STEAL)
   void (*kernel_own)(RenderArgs);  // every lane keeps to its own pixel
+  void (*kernel_pool)(RenderArgs); // per-warp path pool with compacted phases (render_kernel_pool.cuh), or null
 };
+enum RenderSchedule { RS_OWN = 0, RS_STEAL = 1, RS_POOL = 2 };
 const RenderVariant* render_variants_book1(int* n);
 const RenderVariant* render_variants_book2(int* n);
 const RenderVariant* render_variants_book3(int* n);
 
 // Smallest instance of the integrator covering `features` (force_full: the SF_ALL instance).
 const RenderVariant* select_render_variant(int integrator, int features, bool force_full);
-cudaError_t launch_render(const RenderVariant* v, bool steal, const RenderArgs& A, int grid, cudaStream_t st);
-int render_blocks_per_sm(const RenderVariant* v, bool steal);
+cudaError_t launch_render(const RenderVariant* v, int schedule, const RenderArgs& A, int grid, cudaStream_t st);
+int render_blocks_per_sm(const RenderVariant* v, int schedule);
 cudaError_t launch_probe(const ProbeArgs& A, int precision, cudaStream_t st);
 cudaError_t launch_probe64(const ProbeArgs& A, cudaStream_t st);  // probe64.cu (-fmad=false)
 // Tile exchange, last step on the receiving rank: every rank's packed super tiles (rank-major in

@@ -104,7 +104,7 @@ __device__ __forceinline__ void generate_ray(const DevScene& S, const DevCamera&
 // Returns true when the path continues with P.ray replaced, false when it ended (P.L is final).
 template <int INTEGRATOR, int FEAT>
 __device__ __forceinline__ bool shade_step(const DevScene& S, const DevCamera& C, const PathRng& rng, int max_depth,
-                                           Hit32 h, Path& P) {
+                                           Hit32 h, Path& P, const DevPerlin* sh_perlin = nullptr) {
   Ray32& ray = P.ray;
   V3f& T = P.T;
   V3f& L = P.L;
@@ -171,7 +171,7 @@ __device__ __forceinline__ bool shade_step(const DevScene& S, const DevCamera& C
   if ((FEAT & SF_TEXTURES) && M.albedo.w != 0.0f && sf.is_sphere) sphere_uv(sf.n_obj, sf.u, sf.v);
   V3f att(M.albedo.x, M.albedo.y, M.albedo.z);
   const bool textured = M.kind == RRT_M_LAMBERTIAN || M.kind == RRT_M_ISOTROPIC || M.kind == RRT_M_DIFFUSE_LIGHT;
-  if ((FEAT & SF_TEXTURES) && textured && M.tex >= 0) att = texture_value<FEAT>(S, M.tex, sf.u, sf.v, sf.p);
+  if ((FEAT & SF_TEXTURES) && textured && M.tex >= 0) att = texture_value<FEAT>(S, M.tex, sf.u, sf.v, sf.p, sh_perlin);
 
   // Single exit from here on: a `return` inside the material switch or the roulette test would leave
   // the lanes that skip it and the lanes that survive it in separate groups for the rest of the
@@ -298,6 +298,18 @@ render_kernel(const __grid_constant__ RenderArgs A) {
   const int lane = threadIdx.x & 31;
   const int n_items = W.n_tiles * W.chunks;
   const int n_samples = W.s_end - W.s_begin;
+  // Perlin instances: the first Perlin object's tables in shared memory (shade.cuh)
+  __shared__ __align__(16) unsigned char sh_perlin_raw[(FEAT & SF_NOISE) ? sizeof(DevPerlin) : 16];
+  const DevPerlin* sh_perlin = nullptr;
+  if (FEAT & SF_NOISE) {
+    if (S.perlins) {
+      const uint4* src = reinterpret_cast<const uint4*>(S.perlins);
+      uint4* dst = reinterpret_cast<uint4*>(sh_perlin_raw);
+      for (int i = threadIdx.x; i < (int)(sizeof(DevPerlin) / 16); i += RRT_BLOCK) dst[i] = src[i];
+      sh_perlin = reinterpret_cast<const DevPerlin*>(sh_perlin_raw);
+    }
+    __syncthreads();
+  }
 
   for (;;) {
     int item = 0;
@@ -374,7 +386,7 @@ render_kernel(const __grid_constant__ RenderArgs A) {
       Hit32 h;
       h.t = CUDART_INF_F; h.prim = -1;
       world_hit32<FEAT>(S, P.ray, 0.001f, P.skip, h);  // world.hit(r, Interval::new(0.001, INFINITY)), camera.rs:189
-      if (!shade_step<INTEGRATOR, FEAT>(S, C, rng, W.max_depth, h, P)) {
+      if (!shade_step<INTEGRATOR, FEAT>(S, C, rng, W.max_depth, h, P, sh_perlin)) {
         if (finite3(P.L)) {  // a non-finite sample contributes nothing (color.rs:19-27)
           if (!STEAL || tgt == lane) sum = sum + P.L;
           else { atomicAdd(&sh_sum[0][wbase + tgt], P.L.x); atomicAdd(&sh_sum[1][wbase + tgt], P.L.y); atomicAdd(&sh_sum[2][wbase + tgt], P.L.z); }

@@ -19,6 +19,33 @@ namespace rrt {
 #define RRT_PI 3.14159265358979323846f
 
 // ---- Perlin -----------------------------------------------------------------------------------
+// The tables of the scene's first Perlin object are staged in shared memory by the render kernel (4.9 KB:
+// perlin.rs:4-9's 256 gradients + three permutations): 14 table reads per octave, 7 octaves per lookup,
+// and a shared-memory read needs a 32-bit offset where a global one needs 64-bit address arithmetic —
+// a quarter of the 140 instructions of an octave in the global version (profiles/README.md r02a, C3c:
+// 68 % of the kernel is this function).  SHARED selects the address space at compile time.
+template <bool SHARED>
+__device__ __forceinline__ float4 perlin_grad(const DevPerlin* P, int i) {
+  if (SHARED) {
+    float4 g;
+    const unsigned a = (unsigned)__cvta_generic_to_shared(&P->randvec[i]);
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(g.x), "=f"(g.y), "=f"(g.z), "=f"(g.w) : "r"(a));
+    return g;
+  }
+  return ldg4(&P->randvec[i]);
+}
+template <bool SHARED>
+__device__ __forceinline__ int perlin_perm(const DevPerlin* P, int axis, int i) {
+  if (SHARED) {
+    unsigned v;
+    const unsigned a = (unsigned)__cvta_generic_to_shared(&P->perm[axis][i]);
+    asm("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a));
+    return (int)v;
+  }
+  return P->perm[axis][i];
+}
+
+template <bool SHARED>
 __device__ inline float perlin_noise(const DevPerlin* __restrict__ P, V3f p) {
   float fx = floorf(p.x), fy = floorf(p.y), fz = floorf(p.z);
   float u = p.x - fx, v = p.y - fy, w = p.z - fz;
@@ -29,17 +56,17 @@ __device__ inline float perlin_noise(const DevPerlin* __restrict__ P, V3f p) {
   float accum = 0.0f;
 #pragma unroll
   for (int di = 0; di < 2; ++di) {
-    int px = P->perm[0][(i + di) & 255];
+    int px = perlin_perm<SHARED>(P, 0, (i + di) & 255);
     float wi = di ? uu : 1.0f - uu;
 #pragma unroll
     for (int dj = 0; dj < 2; ++dj) {
-      int py = P->perm[1][(j + dj) & 255];
+      int py = perlin_perm<SHARED>(P, 1, (j + dj) & 255);
       float wj = dj ? vv : 1.0f - vv;
 #pragma unroll
       for (int dk = 0; dk < 2; ++dk) {
-        int pz = P->perm[2][(k + dk) & 255];
+        int pz = perlin_perm<SHARED>(P, 2, (k + dk) & 255);
         float wk = dk ? ww : 1.0f - ww;
-        float4 g = ldg4(&P->randvec[px ^ py ^ pz]);
+        float4 g = perlin_grad<SHARED>(P, px ^ py ^ pz);
         float dp = g.x * (u - di) + g.y * (v - dj) + g.z * (w - dk);
         accum += wi * wj * wk * dp;
       }
@@ -48,10 +75,11 @@ __device__ inline float perlin_noise(const DevPerlin* __restrict__ P, V3f p) {
   return accum;
 }
 
+template <bool SHARED>
 __device__ inline float perlin_turb(const DevPerlin* __restrict__ P, V3f p, int depth) {
   float accum = 0.0f, weight = 1.0f;
   for (int i = 0; i < depth; ++i) {
-    accum += weight * perlin_noise(P, p);
+    accum += weight * perlin_noise<SHARED>(P, p);
     weight *= 0.5f;
     p = 2.0f * p;
   }
@@ -59,8 +87,9 @@ __device__ inline float perlin_turb(const DevPerlin* __restrict__ P, V3f p, int 
 }
 
 // ---- textures ---------------------------------------------------------------------------------
+// sh_perlin: the shared-memory copy of S.perlins[0], or null (then every Perlin object is read from global memory)
 template <int FEAT>
-__device__ inline V3f texture_value(const DevScene& S, int tex, float u, float v, V3f p) {
+__device__ inline V3f texture_value(const DevScene& S, int tex, float u, float v, V3f p, const DevPerlin* sh_perlin) {
   for (int guard = 0; guard < 9; ++guard) {
     const DevTexture t = S.textures[tex];
     if (t.kind == RRT_T_CHECKER) {  // texture.rs:63-77
@@ -84,7 +113,7 @@ __device__ inline V3f texture_value(const DevScene& S, int tex, float u, float v
     }
     // NoiseTexture, texture.rs:121-126
     if (!(FEAT & SF_NOISE)) return V3f(0.0f, 0.0f, 0.0f);  // unreachable: the flattener sets SF_NOISE for such scenes
-    float turb = perlin_turb(S.perlins + t.a, p, 7);
+    const float turb = (sh_perlin && t.a == 0) ? perlin_turb<true>(sh_perlin, p, 7) : perlin_turb<false>(S.perlins + t.a, p, 7);
     float c = 0.5f * (1.0f + sinf(t.v.w * p.z + 10.0f * turb));
     return V3f(c, c, c);
   }

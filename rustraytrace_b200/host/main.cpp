@@ -13,6 +13,8 @@
 #include <string>
 #include <vector>
 
+#include <unistd.h>
+
 #include "../../include/rrt.h"
 #include "../../include/rrt_host.h"
 
@@ -112,6 +114,13 @@ int main(int argc, char** argv) {
   }
   const rrt_camera* cam = rrth_scene_camera(hs);
   const int W = cam->image_width, H = rrt_image_height(cam);
+  // stdout is the image (render_io.rs:3-30 prints the PPM there).  Libraries under us may print too —
+  // NCCL's version banner goes to stdout whenever NCCL_DEBUG is set in the environment — so everything
+  // between here and the PPM is sent to stderr and the real stdout is put back for the image alone.
+  std::fflush(stdout);
+  const int saved_stdout = dup(1);
+  dup2(2, 1);
+  auto restore_stdout = [&]() { std::fflush(stdout); if (saved_stdout >= 0) dup2(saved_stdout, 1); };
   rrt_ctx* ctx = nullptr;
   const int init_rc = devices.empty() ? rrt_init(device, &ctx) : rrt_init_multi(devices.data(), (int)devices.size(), &ctx);
   if (init_rc != RRT_OK) {
@@ -128,6 +137,7 @@ int main(int argc, char** argv) {
       std::fprintf(stderr, "CUDA render failed: %s\n", rrt_last_error());
       rc = 1;
     } else {
+      restore_stdout();
       FILE* f = out_path ? std::fopen(out_path, "w") : stdout;
       if (!f) { std::perror(out_path); rc = 1; }
       else {
@@ -154,6 +164,7 @@ int main(int argc, char** argv) {
       rrt_get_stats(ctx, &st);
       std::fprintf(stderr, "Done: %.0f paths in %.1f ms (%.1f Mpaths/s), %d prims, %d BVH nodes, %d GPU(s), exchange %.2f ms\n", st.paths,
                    st.kernel_ms, st.paths / st.kernel_ms / 1e3, st.n_prims, st.n_bvh_nodes, st.n_devices, st.exchange_ms);
+      restore_stdout();
       if (rrth_write_ppm_from_accum(out_path, W, H, accum.data(), (uint32_t)st.spp_effective) != 0) {
         std::fprintf(stderr, "could not write the image: %s\n", rrth_last_error());
         rc = 1;

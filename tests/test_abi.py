@@ -181,13 +181,56 @@ def test_image_height_truncates_like_camera_initialize():
         assert F.rrt().rrt_image_height(C.byref(cam)) == h
 
 
+C_TO_RUST = {"int32_t": "i32", "uint64_t": "u64", "uint32_t": "u32", "double": "f64", "float": "f32", "int": "i32"}
+
+
+def c_struct_fields(header_text, name):
+    """[(field, rust type)] of `typedef struct name { ... } name;` in a C header (arrays and pointers included)."""
+    body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (name, name), header_text, re.S).group(1)
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    out = []
+    for decl in body.split(";"):
+        decl = " ".join(decl.split())
+        if not decl:
+            continue
+        m = re.match(r"(const )?(\w+)(\*?) (.+)$", decl)
+        const, ctype, star, names = m.groups()
+        for nm in names.split(","):
+            nm = nm.strip()
+            ptr = star == "*" or nm.startswith("*")
+            nm = nm.lstrip("*")
+            dims = [int(d) for d in re.findall(r"\[(\d+)\]", nm)]
+            nm = nm.split("[")[0]
+            base = C_TO_RUST.get(ctype) or "Rrt" + "".join(w.capitalize() for w in ctype.split("_")[1:])
+            if ctype == "uint8_t":
+                base = "u8"
+            ty = base
+            for d in reversed(dims):
+                ty = f"[{ty}; {d}]"
+            if ptr:
+                ty = f"*const {ty}"
+            out.append((nm, ty))
+    return out
+
+
 def test_rust_binding_declares_every_entry_point():
-    """bindings/rrt_ffi.rs (unbuilt here: no rustc) must name every function of include/rrt.h."""
+    """bindings/rrt_ffi.rs (unbuilt here: no rustc) must name every function of include/rrt.h, and its
+    #[repr(C)] structs must list the header's fields in the header's order with the matching Rust types."""
     rs = open(os.path.join(ROOT, "bindings", "rrt_ffi.rs")).read()
+    hdr = open(os.path.join(ROOT, "include", "rrt.h")).read()
     for n in declared("rrt.h"):
         assert re.search(r"pub fn %s\(" % n, rs), f"{n} missing from bindings/rrt_ffi.rs"
-    # #[repr(C)] mirrors carry the same field counts as the ctypes mirrors (which are size-checked above)
-    for rust, py in [("RrtHittable", F.Hittable), ("RrtMaterial", F.Material), ("RrtTexture", F.Texture),
-                     ("RrtCamera", F.Camera), ("RrtRenderParams", F.RenderParams), ("RrtStats", F.Stats)]:
-        body = re.search(r"pub struct %s \{(.*?)\}" % rust, rs, re.S).group(1)
-        assert len(re.findall(r"pub \w+:", body)) == len(py._fields_), rust
+    for cname, rust in [("rrt_hittable", "RrtHittable"), ("rrt_material", "RrtMaterial"), ("rrt_texture", "RrtTexture"),
+                        ("rrt_image", "RrtImage"), ("rrt_perlin", "RrtPerlin"), ("rrt_scene_desc", "RrtSceneDesc"),
+                        ("rrt_camera", "RrtCamera"), ("rrt_render_params", "RrtRenderParams"), ("rrt_stats", "RrtStats")]:
+        body = re.search(r"pub struct %s \{(.*?)\}\n" % rust, rs, re.S).group(1)
+        got = [(a, " ".join(b.split())) for a, b in re.findall(r"pub (\w+): ([^,}]+?)\s*(?:,|$)", body.replace("\n", " "))]
+        want = c_struct_fields(hdr, cname)
+        assert got == want, (rust, got, want)
+    # the flattener and the call site are complete files: every helper they call exists
+    fl = open(os.path.join(ROOT, "bindings", "flatten.rs")).read()
+    for fn in ("hittable", "container", "material", "texture", "image", "perlin", "finish"):
+        assert re.search(r"fn %s\(" % fn, fl), fn
+    assert "pub struct Keep" in fl
+    cs = open(os.path.join(ROOT, "bindings", "call_site.rs")).read()
+    assert "pub fn render_with_rrt(" in cs and "-> Result<(), String>" in cs and "rrt_init_multi" in cs

@@ -237,3 +237,71 @@ def test_front_run_changes_nothing_but_the_tree(ctx, book, scene_no, monkeypatch
     assert np.array_equal(ids32, pids32) and np.array_equal(t32, pt32)
     assert np.array_equal(a[..., 3], b[..., 3])
     assert np.allclose(a[..., :3], b[..., :3], rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("book,scene_no", [("in_one_weekend", None), ("the_next_week", 1), ("the_next_week", 9), ("the_rest_of_your_life", None)])
+def test_pool_schedule_renders_the_same_frame(ctx, book, scene_no, monkeypatch):
+    """RRT_POOL=1: the per-warp path pool with compacted regenerate / traverse / shade phases
+    (render_kernel_pool.cuh), the measured alternative to the lane-per-pixel megakernel
+    (profiles/README.md r02h: it loses 3-10 %).  Same Philox keys, same functions below the schedule:
+    every pixel gets its samples and the frame is the default one — up to float summation order and, as
+    between any two instances of the kernel, the compiler's different FMA contraction, which lets a handful
+    of deep paths flip at a boundary (measured: identical at depth 1-2, 0.7-1.7 % of the pixels hold one
+    different path at depth 10)."""
+    s = R.BookScene(book, scene_no, overrides=dict(image_width=100, samples_per_pixel=49, max_depth=10))
+    gs = ctx.scene(s.desc)
+    a = ctx.render(gs, s.camera, s.integrator, seed=9).astype(np.float64)
+    gs.close()
+    monkeypatch.setenv("RRT_POOL", "1")
+    pool = R.Context(0)
+    monkeypatch.delenv("RRT_POOL")
+    gp = pool.scene(s.desc)
+    b = pool.render(gp, s.camera, s.integrator, seed=9).astype(np.float64)
+    gp.close(); pool.close()
+    assert np.all(a[..., 3] == 49) and np.all(b[..., 3] == 49)
+    ma, mb = a[..., :3].mean(axis=(0, 1)), b[..., :3].mean(axis=(0, 1))
+    assert np.all(np.abs(ma - mb) <= 1e-3 * mb), (ma, mb)
+    lum_a, lum_b = a[..., :3].sum(axis=2), b[..., :3].sum(axis=2)
+    assert (np.abs(lum_a - lum_b) > 1e-3 * np.maximum(lum_b, 1e-3)).mean() < 0.05
+
+
+def test_deterministic_switch_repeats_bit_for_bit(monkeypatch):
+    """RRT_DETERMINISTIC=1 (include/rrt.h): no sample stealing, one work item per tile — each pixel is one
+    lane's sum in sample order and one float4 store, so two renders are identical to the last bit (the
+    default schedule adds per-chunk sums with float atomics in completion order and may differ in the
+    last ulps), and the result is the default frame up to summation order."""
+    s = R.BookScene("the_next_week", 1, overrides=dict(image_width=160, samples_per_pixel=64, max_depth=12))
+    monkeypatch.setenv("RRT_DETERMINISTIC", "1")
+    det = R.Context(0)
+    monkeypatch.delenv("RRT_DETERMINISTIC")
+    gs = det.scene(s.desc)
+    a = det.render(gs, s.camera, s.integrator, seed=4)
+    b = det.render(gs, s.camera, s.integrator, seed=4)
+    gs.close(); det.close()
+    assert np.array_equal(a, b)
+    c = R.Context(0)
+    g2 = c.scene(s.desc)
+    d = c.render(g2, s.camera, s.integrator, seed=4)
+    g2.close(); c.close()
+    assert np.allclose(a, d, rtol=1e-4, atol=1e-4)
+
+
+def test_depth_zero_is_black_like_the_reference(ctx):
+    """ray_color(r, depth <= 0) returns black (camera.rs:185-187): max_depth 0 gives a black frame whose .w
+    still counts the samples — not the background colour."""
+    s = R.BookScene("the_next_week", 1, overrides=dict(image_width=64, samples_per_pixel=8, max_depth=0))
+    gs = ctx.scene(s.desc)
+    acc = ctx.render(gs, s.camera, s.integrator, seed=1)
+    gs.close()
+    assert np.all(acc[..., :3] == 0) and np.all(acc[..., 3] == 8)
+
+
+def test_oversized_frames_and_too_deep_trees_are_refused(ctx):
+    b = R.DescBuilder()
+    d = b.desc(b.list([b.sphere((0, 0, -1), 0.5, b.lambertian((0.5, 0.5, 0.5)))]))
+    gs = ctx.scene(d)
+    cam = R.make_camera(image_width=65536, aspect_ratio=1.0)            # 2^32 pixels
+    with pytest.raises(R.RrtError) as e:
+        ctx.render(gs, cam, F.INT_BOOK1)
+    assert e.value.status == F.ERR_INVALID and "2^30" in str(e.value)
+    gs.close()
