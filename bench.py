@@ -370,7 +370,9 @@ def main():
         achieved = (head["my_paths_per_step"] * f_path / (k_ms * 1e-3) / 1e12) if f_path else None
         traffic, traffic_src = None, None
         import glob
-        caps = sorted(glob.glob(os.path.join(ROOT, "profiles", "ncu_r*_render_kernel_c2_spp64.csv")))
+        # ncu_r<round><letter>_render_kernel_c2_spp64.csv only: captures of experiments carry a tag (ncu_r02h_pool_..., _bvh4_...)
+        caps = sorted(p for p in glob.glob(os.path.join(ROOT, "profiles", "ncu_r*_render_kernel_c2_spp64.csv"))
+                      if os.path.basename(p).split("_")[2] == "render")
         ncu_csv = caps[-1] if caps else ""   # the newest capture (names sort by round)
         if args.config == "C2" and ncu_csv:   # the committed `ncu --set full` capture of this kernel
             tot = 0.0

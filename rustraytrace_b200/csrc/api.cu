@@ -168,7 +168,7 @@ int rrt::render_enqueue(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, 
   // Sample stealing (render_kernel.cuh) pays wherever path cost varies inside a warp (C1 +20 %, C2/C3a
   // +3.5 %, C5 +1-6 %).  Not for one- and two-primitive scenes (near-constant path cost; the shared
   // counters cost 9 % on C3b) nor for the Perlin instances, which sit at their register limit (C4 -4 %).
-  const bool steal = sc->n_prims > 2 && !(variant->features & SF_NOISE) && !c->no_steal && !c->deterministic;
+  const bool steal = sc->n_prims > 2 && (!(variant->features & SF_NOISE) || c->force_steal) && !c->no_steal && !c->deterministic;
   const int schedule = c->use_pool && variant->kernel_pool && !c->deterministic ? RS_POOL : steal ? RS_STEAL : RS_OWN;
   int bps = render_blocks_per_sm(variant, schedule);
   if (bps < 1) return fail(RRT_ERR_CUDA, "kernel launch failed: render kernel does not fit on an SM");
@@ -253,6 +253,7 @@ static int init_device_ctx(int device, rrt_ctx** out) {
   const char* kv = std::getenv("RRT_KERNEL");
   c->force_full_kernel = kv && std::strcmp(kv, "full") == 0;
   c->no_steal = std::getenv("RRT_NO_STEAL") != nullptr;
+  c->force_steal = std::getenv("RRT_FORCE_STEAL") != nullptr;
   c->deterministic = std::getenv("RRT_DETERMINISTIC") != nullptr;
   c->use_pool = std::getenv("RRT_POOL") != nullptr;
   e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking);

@@ -33,6 +33,7 @@ struct rrt_ctx {
   size_t accum_floats = 0;
   rrt_stats stats;
   bool no_steal = false;              // RRT_NO_STEAL=1: lanes never take over neighbours' samples (debugging / A-B)
+  bool force_steal = false;           // RRT_FORCE_STEAL=1: stealing also in the Perlin instances (A-B)
   bool deterministic = false;         // RRT_DETERMINISTIC=1: no stealing, one chunk per tile -> bit-reproducible frames
   bool use_pool = false;              // RRT_POOL=1: the per-warp path-pool schedule where an instance has it (render_kernel_pool.cuh)
   bool force_full_kernel = false;     // RRT_KERNEL=full: always run the SF_ALL render kernel instance (include/rrt.h)

@@ -425,6 +425,7 @@ struct Builder {
   std::vector<BNode> nodes;
   int max_leaf;
   int max_depth_seen = 0;
+  bool pair_leaves = false;   // two spheres left: one leaf (tested as a packed pair), whatever SAH says
 
   Builder(const std::vector<BakedPrim>& p, int ml) : P(p), max_leaf(ml) {
     order.resize(P.size());
@@ -456,6 +457,7 @@ struct Builder {
     bounds(first, count, nodes[me].lo, nodes[me].hi);
     nodes[me].first = first; nodes[me].count = count;
     if (count <= 1 || (count <= max_leaf && depth >= 40 && leaf_ok(first, count))) return me;
+    if (pair_leaves && count == 2 && P[order[first]].kind == PRIM_SPHERE && P[order[first + 1]].kind == PRIM_SPHERE) return me;
     double parent_area = area(nodes[me].lo, nodes[me].hi);
     double best_cost = std::numeric_limits<double>::infinity();
     int best_axis = -1, best_split = -1;
@@ -786,6 +788,7 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
   std::vector<BakedPrim> front(items.begin(), items.begin() + n_front);
   items.erase(items.begin(), items.begin() + n_front);
   Builder B(items, single ? (int)items.size() : max_leaf);
+  B.pair_leaves = std::getenv("RRT_PAIR_LEAVES") != nullptr;
   int root = 0;
   if (single) {
     B.nodes.push_back(BNode());

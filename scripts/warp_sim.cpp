@@ -70,6 +70,8 @@ struct Tree {
   FlatScene F;
   std::vector<int> id_to_flat;           // construction id -> flat prim index (for `skip`)
   bool chain = true;                     // sphere-only instances run consecutive leaves in one round
+  bool inline_box = false;
+  bool chain_spheres_only = false;
   int defer = 1;                         // leaves a lane puts aside before it waits for a leaf round (1 = the kernel)
 };
 
@@ -139,7 +141,7 @@ Hit world_hit(const Tree& T, const Ray& r, float tmin, int skip, Trace* tr) {
   const float id[3] = {rcp(r.d.x), rcp(r.d.y), rcp(r.d.z)};
   const float oo[3] = {r.o.x * id[0], r.o.y * id[1], r.o.z * id[2]};
   int stack[64], sp = 0;
-  auto count = [](int ref) { const int lf = ~ref; return (lf & 0xFF) == LEAF_BOX_MARK ? 3 : ((lf >> 4) & 15) + (lf & 15); };  // primitives tested (a box leaf ~ 3: slab test, entry face, fall-back)
+  auto count = [](int ref) { const int lf = ~ref; return (lf & 0xFF) == LEAF_BOX_MARK ? 3 : ((lf >> 4) & 15) + (lf & 15); };  // (a packed sphere pair: 2 here, priced by SIM_C_PAIR below)  // primitives tested (a box leaf ~ 3: slab test, entry face, fall-back)
   for (;;) {
     bool done = false;
     int steps = 0, leaves = 0, buf[8], nb = 0;
@@ -169,6 +171,12 @@ Hit world_hit(const Tree& T, const Ray& r, float tmin, int skip, Trace* tr) {
         else { if (sp == 0) { done = true; break; } cur = stack[--sp]; }
       }
       if (done) break;
+      if (T.inline_box && ((~cur) & 0xFF) == LEAF_BOX_MARK) {   // SIM_INLINE_BOX: a box leaf is settled by its parent's slab test, no leaf round
+        leaf_hit(F, ~cur, r, a, inv_a, tmin, skip, h);
+        if (sp == 0) { done = true; break; }
+        cur = stack[--sp];
+        continue;
+      }
       buf[nb++] = cur;
       if (nb >= T.defer) break;
       if (sp == 0) { done = true; break; }
@@ -180,6 +188,7 @@ Hit world_hit(const Tree& T, const Ray& r, float tmin, int skip, Trace* tr) {
         if (sp == 0) { done = true; break; }
         cur = stack[--sp];
         if (!(T.chain && T.defer == 1 && cur < 0)) break;
+        if (T.chain_spheres_only && ((~cur) & 0xFF) == LEAF_BOX_MARK) break;   // SIM_CHAIN=s: only sphere/quad leaves are chained
         leaves += count(cur); leaf_hit(F, ~cur, r, a, inv_a, tmin, skip, h);   // consecutive leaves in one round
       }
     }
@@ -266,6 +275,8 @@ int main(int argc, char** argv) {
   const int single_max = std::getenv("SIM_SINGLE_LEAF_MAX") ? std::atoi(std::getenv("SIM_SINGLE_LEAF_MAX")) : RRT_SINGLE_LEAF_MAX;
   if (flatten_scene(desc, T.F, err, single_max, max_leaf) != RRT_OK) { std::fprintf(stderr, "flatten: %s\n", err.c_str()); return 1; }
   T.chain = (!(T.F.features & SF_QUADS) || std::getenv("SIM_CHAIN")) && !std::getenv("SIM_NO_CHAIN");
+  T.inline_box = std::getenv("SIM_INLINE_BOX") != nullptr;
+  T.chain_spheres_only = std::getenv("SIM_CHAIN") && std::getenv("SIM_CHAIN")[0] == 's';
   if (std::getenv("SIM_DEFER")) T.defer = std::min(8, std::max(1, std::atoi(std::getenv("SIM_DEFER"))));
   // the rays come from a fixed tree, so that every variant is scored on the same segments
   Tree B;
@@ -406,6 +417,75 @@ int main(int argc, char** argv) {
     }
     rounds += R;
     cost += c;
+  }
+  // ---- SIM_QUEUE=1: the same rays through a decoupled traversal (a pool of rays, any lane takes the next
+  // one as soon as its own is finished; rounds as in the kernel: descend to a leaf, leaf round) -----------
+  if (std::getenv("SIM_QUEUE")) {
+    const double C_FETCH = std::getenv("SIM_C_FETCH") ? std::atof(std::getenv("SIM_C_FETCH")) : 20, C_DONE = 8;
+    const double C_SHADE = C_SETUP + C_FIXED + 40;   // per 32 segments, converged, + state traffic
+    std::vector<Trace> all;
+    double fronts = 0;
+    // SIM_SORT=w: rays sorted inside windows of w by (direction octant, origin cell) before they are handed out
+    std::vector<Seg> segs;
+    for (const Iter& it : iters) for (const Seg& s : it.lanes) segs.push_back(s);
+    if (const char* e = std::getenv("SIM_SORT")) {
+      const size_t w = (size_t)std::atoi(e);
+      float lo[3] = {1e30f, 1e30f, 1e30f}, hi[3] = {-1e30f, -1e30f, -1e30f};
+      for (const Seg& s : segs) { const float o[3] = {s.r.o.x, s.r.o.y, s.r.o.z}; for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], o[a]); hi[a] = std::max(hi[a], o[a]); } }
+      auto key = [&](const Seg& s) {
+        const float o[3] = {s.r.o.x, s.r.o.y, s.r.o.z};
+        unsigned k = (s.r.d.x < 0) | ((s.r.d.y < 0) << 1) | ((s.r.d.z < 0) << 2);
+        unsigned c[3];
+        for (int a = 0; a < 3; ++a) c[a] = (unsigned)std::min(15.0f, 16.0f * (o[a] - lo[a]) / std::max(1e-9f, hi[a] - lo[a]));
+        unsigned m = 0;
+        for (int b = 3; b >= 0; --b) for (int a = 0; a < 3; ++a) m = (m << 1) | ((c[a] >> b) & 1);
+        return (k << 12) | m;
+      };
+      for (size_t i = 0; i < segs.size(); i += w)
+        std::stable_sort(segs.begin() + i, segs.begin() + std::min(segs.size(), i + w), [&](const Seg& a, const Seg& b) { return key(a) < key(b); });
+    }
+    for (int once = 0; once < 1; ++once)
+      for (const Seg& s : segs) {
+        Trace t2;
+        const int skip = s.skip_id >= 0 ? T.id_to_flat[s.skip_id] : -1;
+        world_hit(T, s.r, 0.001f, skip, &t2);
+        fronts += t2.front_tests;
+        all.push_back(std::move(t2));
+      }
+    const int pool = std::getenv("SIM_POOL") ? std::atoi(std::getenv("SIM_POOL")) : 1 << 30;   // rays per phase (tail at the end of each)
+    double qcost = 0, qsteps = 0, lane_active = 0;
+    size_t next = 0;
+    while (next < all.size()) {
+      const size_t end = std::min(all.size(), next + (size_t)pool);
+      int cur[32], rnd[32];
+      for (int l = 0; l < 32; ++l) cur[l] = -1;
+      for (;;) {
+        bool fetched = false, any = false;
+        for (int l = 0; l < 32; ++l) {
+          while (cur[l] < 0 && next < end) {   // rays with no rounds at all (front run settles them) finish at once
+            cur[l] = (int)next++; rnd[l] = 0; fetched = true;
+            if (all[cur[l]].steps.empty()) cur[l] = -1;
+          }
+          any |= cur[l] >= 0;
+        }
+        if (fetched) qcost += C_FETCH;
+        if (!any) break;
+        int ms = 0, ml = 0, act = 0; bool fin = false;
+        for (int l = 0; l < 32; ++l) if (cur[l] >= 0) {
+          const Trace& t2 = all[cur[l]];
+          ms = std::max<int>(ms, t2.steps[rnd[l]]); ml = std::max<int>(ml, t2.leaves[rnd[l]]);
+          lane_active += t2.steps[rnd[l]]; ++act;
+          if (++rnd[l] >= (int)t2.steps.size()) { cur[l] = -1; fin = true; }
+        }
+        qsteps += ms;
+        qcost += C_NODE * ms + (ml ? C_LEAF_ROUND + C_LEAF * ml : 0) + (fin ? C_DONE : 0);
+      }
+    }
+    const double nseg = (double)all.size();
+    const double front_cost = C_FRONT * (fronts / nseg) * nseg / 32.0, shade_cost = C_SHADE * nseg / 32.0;
+    std::printf("QUEUE model (pool %d): traversal %.0f + front %.0f + shade/regen %.0f = %.0f warp instructions per 32 segments; node steps per 32 segments %.2f (lane occupancy %.0f %%)\n",
+                pool, 32 * qcost / nseg, 32 * front_cost / nseg, 32 * shade_cost / nseg, 32 * (qcost + front_cost + shade_cost) / nseg, 32 * qsteps / nseg, 100.0 * lane_active / (32.0 * qsteps));
+    std::printf("QUEUE vs kernel, warp instructions per segment-lane: %.1f vs %.1f\n", (qcost + front_cost + shade_cost) / nseg, cost / lanes);
   }
   const double ni = (double)iters.size();
   std::printf("scene book %d/%d width %d: %d prims, %zu nodes, front run %d, chain %d | %.0f paths, %.2f segments per path, %.1f lanes per warp iteration\n",
