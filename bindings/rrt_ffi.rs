@@ -31,7 +31,7 @@ pub struct RrtRenderParams { pub integrator: i32, pub shard_mode: i32, pub rank:
 pub struct RrtStats { pub width: i32, pub height: i32, pub spp_effective: i32, pub kernel_launches: i32,
                       pub paths: f64, pub kernel_ms: f64, pub total_ms: f64, pub h2d_bytes: u64, pub d2h_bytes: u64,
                       pub n_prims: i32, pub n_bvh_nodes: i32, pub n_media: i32, pub n_lights: i32, pub sm_count: i32, pub kernel_features: i32,
-                      pub n_devices: i32, pub _pad: i32, pub exchange_ms: f64 }
+                      pub n_devices: i32, pub n_grid_cells: i32, pub exchange_ms: f64 }
 #[repr(C)] pub struct RrtCtx { _p: [u8; 0] }
 #[repr(C)] pub struct RrtScene { _p: [u8; 0] }
 
@@ -60,6 +60,7 @@ extern "C" {
     pub fn rrt_flatten_check(desc: *const RrtSceneDesc, n_prims: *mut i32, n_nodes: *mut i32, bvh_depth: *mut i32,
                              n_media: *mut i32, n_lights: *mut i32) -> c_int;
     pub fn rrt_scene_features(desc: *const RrtSceneDesc, features: *mut i32) -> c_int;
+    pub fn rrt_flatten_grid(desc: *const RrtSceneDesc, res3: *mut i32, n_refs: *mut i32, max_per_cell: *mut i32) -> c_int;
     pub fn rrt_philox_kat(c0: u32, c1: u32, c2: u32, c3: u32, k0: u32, k1: u32, out4: *mut u32);
     pub fn rrt_philox_kat_rounds(rounds: c_int, c0: u32, c1: u32, c2: u32, c3: u32, k0: u32, k1: u32, out4: *mut u32) -> c_int;
     pub fn rrt_philox_rounds() -> c_int;

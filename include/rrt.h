@@ -173,7 +173,8 @@ typedef struct rrt_stats {
                             * 5 box leaves (63 = the general instance); a scene runs on the smallest instance covering it.
                             * RRT_KERNEL=full in the environment at rrt_init forces 63 (debugging). */
   int32_t n_devices;       /* GPUs behind the last call: 1, the size of an rrt_init_multi group, or the communicator's world */
-  int32_t _pad;
+  int32_t n_grid_cells;    /* cells of the uniform grid the scene's sphere field is walked through, or 0: the BVH
+                            * (an even field of spheres gets a grid next to its BVH; RRT_NO_GRID=1 at rrt_scene_create keeps the BVH) */
   double exchange_ms;      /* device time of the frame exchange after the kernels (NCCL reduce, or gather of owned tiles
                             * + scatter into the frame) on the rank that receives it; 0 on one GPU.  With several GPUs
                             * kernel_ms is the slowest member's kernel and paths counts every member's. */
@@ -191,7 +192,9 @@ typedef struct rrt_scene rrt_scene;
  *                          schedule adds per-chunk sums with float atomics in whatever order they finish)
  *   RRT_NO_BOX_LEAVES=1    (rrt_scene_create) axis-aligned boxes stay six separate quad leaves
  *   RRT_NO_FRONT=1         (rrt_scene_create) outsized primitives (a ground sphere) stay in the BVH instead of
- *                          being tested ahead of the traversal */
+ *                          being tested ahead of the traversal
+ *   RRT_NO_GRID=1          (rrt_scene_create) an even field of spheres is walked through its BVH, not its grid
+ *   RRT_FORCE_GRID=1       (rrt_scene_create) a grid for every sphere-only tree, however uneven */
 int rrt_init(int device, rrt_ctx** out);
 void rrt_shutdown(rrt_ctx* ctx);
 
@@ -299,6 +302,9 @@ int rrt_shard_plan(const rrt_camera* cam, const rrt_render_params* params, int32
 int rrt_flatten_check(const rrt_scene_desc* desc, int32_t* n_prims, int32_t* n_nodes, int32_t* bvh_depth,
                       int32_t* n_media, int32_t* n_lights);
 int rrt_scene_features(const rrt_scene_desc* desc, int32_t* features);
+/*   rrt_flatten_grid: the uniform grid the flattener lays over an even field of spheres (rrt_stats.n_grid_cells):
+ *   cells per axis (0, 0, 0: the scene is walked through its BVH), references in all cells, most in one cell. */
+int rrt_flatten_grid(const rrt_scene_desc* desc, int32_t res3[3], int32_t* n_refs, int32_t* max_per_cell);
 void rrt_philox_kat(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1,
                     uint32_t* out4);
 /*   rrt_philox_kat_rounds: the same block at 7 or 10 rounds (Random123 publishes known answers for both);

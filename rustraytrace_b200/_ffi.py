@@ -68,7 +68,7 @@ class Stats(C.Structure):
                 ("paths", c_dbl), ("kernel_ms", c_dbl), ("total_ms", c_dbl),
                 ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
                 ("n_prims", c_int), ("n_bvh_nodes", c_int), ("n_media", c_int), ("n_lights", c_int),
-                ("sm_count", c_int), ("kernel_features", c_int), ("n_devices", c_int), ("_pad", c_int),
+                ("sm_count", c_int), ("kernel_features", c_int), ("n_devices", c_int), ("n_grid_cells", c_int),
                 ("exchange_ms", c_dbl)]
 
 
@@ -116,6 +116,7 @@ RRT_SYMBOLS = [
                                C.POINTER(c_int), C.POINTER(c_dbl), VP]),
     ("rrt_flatten_check", c_int, [C.POINTER(SceneDesc)] + [C.POINTER(c_int)] * 5),
     ("rrt_scene_features", c_int, [C.POINTER(SceneDesc), C.POINTER(c_int)]),
+    ("rrt_flatten_grid", c_int, [C.POINTER(SceneDesc), C.POINTER(c_int * 3), C.POINTER(c_int), C.POINTER(c_int)]),
     ("rrt_philox_kat", None, [C.c_uint32] * 6 + [C.POINTER(C.c_uint32)]),
     ("rrt_philox_kat_rounds", c_int, [c_int] + [C.c_uint32] * 6 + [C.POINTER(C.c_uint32)]),
     ("rrt_philox_rounds", c_int, []),

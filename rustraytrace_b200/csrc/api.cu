@@ -75,7 +75,7 @@ int rrt::scene_upload(rrt_ctx* c, const FlatScene& F, rrt_scene** out) {
       (rc = upload(sc, F.materials, &D.materials)) || (rc = upload(sc, F.textures, &D.textures)) ||
       (rc = upload(sc, F.images, &D.images)) || (rc = upload(sc, F.texels, &texels)) ||
       (rc = upload(sc, F.perlins, &D.perlins)) || (rc = upload(sc, F.media, &D.media)) ||
-      (rc = upload(sc, F.lights, &D.lights))) {
+      (rc = upload(sc, F.lights, &D.lights)) || (rc = upload(sc, F.grid_cells, &D.grid_cells)) || (rc = upload(sc, F.grid_refs, &D.grid_refs))) {
     scene_release(sc); delete sc;
     return rc;
   }
@@ -88,7 +88,9 @@ int rrt::scene_upload(rrt_ctx* c, const FlatScene& F, rrt_scene** out) {
   D.n_lights = (int)F.lights.size();
   D.has_motion = F.has_motion;
   D.features = F.features;
+  for (int a = 0; a < 3; ++a) { D.glo[a] = F.glo[a]; D.ghi[a] = F.ghi[a]; D.gcell[a] = F.gcell[a]; D.ginv[a] = F.ginv[a]; D.gres[a] = F.gres[a]; }
   sc->n_nodes = D.n_nodes; sc->n_prims = D.n_prims; sc->n_media = D.n_media; sc->n_lights = D.n_lights;
+  sc->n_grid_cells = (int)F.grid_cells.size();
   cudaError_t e = cudaStreamSynchronize(c->stream);  // the host vectors die when the caller returns
   if (e != cudaSuccess) { scene_release(sc); delete sc; return fail(RRT_ERR_CUDA, std::string("scene upload: ") + cudaGetErrorString(e)); }
   c->scenes.push_back(sc);
@@ -130,6 +132,7 @@ static void plan_work(const rrt_camera* cam, const rrt_render_params* p, DevWork
   W.rank = p->shard_mode == RRT_SHARD_NONE ? 0 : p->rank;
   W.world = p->shard_mode == RRT_SHARD_NONE ? 1 : p->world;
   W.seed_lo = (unsigned)(p->seed & 0xffffffffu); W.seed_hi = (unsigned)(p->seed >> 32);
+  philox_round_keys(W.seed_lo, W.seed_hi, W.rkeys, 10);
   int spp_eff = cam->samples_per_pixel;
   if (p->integrator == RRT_INT_BOOK3) spp_eff = dc.sqrt_spp * dc.sqrt_spp;  // camera.rs:114-116
   W.spp_eff = spp_eff;
@@ -220,6 +223,7 @@ void rrt::stats_from_share(rrt_ctx* c, const rrt_scene* sc, const ShareInfo& s) 
   st.exchange_ms = 0; st.n_devices = 1;
   st.d2h_bytes = 0;
   st.n_prims = sc->n_prims; st.n_bvh_nodes = sc->n_nodes; st.n_media = sc->n_media; st.n_lights = sc->n_lights;
+  st.n_grid_cells = sc->n_grid_cells;
   st.sm_count = c->sm_count;
   st.kernel_features = s.features;
 }
@@ -384,6 +388,7 @@ int rrt_scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out) {
   c->stats.h2d_bytes = sc->h2d_bytes;
   c->stats.n_prims = p0->n_prims; c->stats.n_bvh_nodes = p0->n_nodes;
   c->stats.n_media = p0->n_media; c->stats.n_lights = p0->n_lights;
+  c->stats.n_grid_cells = p0->n_grid_cells;
   *out = sc;
   return RRT_OK;
 }
@@ -630,6 +635,20 @@ extern "C" int rrt_scene_features(const rrt_scene_desc* desc, int32_t* features)
   return RRT_OK;
 }
 
+extern "C" int rrt_flatten_grid(const rrt_scene_desc* desc, int32_t res3[3], int32_t* n_refs, int32_t* max_per_cell) {
+  FlatScene F;
+  std::string err;
+  int st = flatten_scene(desc, F, err);
+  if (st != RRT_OK) return fail(st, "scene flatten failed: " + err);
+  int most = 0;
+  for (unsigned h : F.grid_cells) most = std::max(most, (int)(h & 255u));
+  const bool on = !F.grid_cells.empty();
+  if (res3) for (int a = 0; a < 3; ++a) res3[a] = on ? F.gres[a] : 0;
+  if (n_refs) *n_refs = on ? (int)F.grid_refs.size() : 0;
+  if (max_per_cell) *max_per_cell = most;
+  return RRT_OK;
+}
+
 extern "C" int rrt_flatten_check(const rrt_scene_desc* desc, int32_t* n_prims, int32_t* n_nodes, int32_t* bvh_depth,
                                  int32_t* n_media, int32_t* n_lights) {
   FlatScene F;
@@ -683,6 +702,41 @@ extern "C" int rrt_flatten_check(const rrt_scene_desc* desc, int32_t* n_prims, i
   }
   for (int i = 0; i < F.n_prims; ++i)
     if (seen[i] != 1) return fail(RRT_ERR_INVALID, "flatten check: primitive not in exactly one leaf");
+  // the grid of a sphere field: every reference in range, every sphere of the tree referenced from every cell
+  // its box overlaps (so that a walk through the cells cannot miss it), nothing else referenced
+  if (!F.grid_cells.empty()) {
+    const size_t n_cells = (size_t)F.gres[0] * F.gres[1] * F.gres[2];
+    if (F.gres[0] < 1 || F.gres[1] < 1 || F.gres[2] < 1 || n_cells != F.grid_cells.size())
+      return fail(RRT_ERR_INVALID, "flatten check: grid resolution does not match its cell table");
+    std::vector<char> in_front(F.n_prims, 0);
+    { const int lf = ~F.front_ref, first = lf >> 8, n = ((lf >> 4) & 15) + (lf & 15); for (int k = 0; k < n; ++k) in_front[first + k] = 1; }
+    for (size_t c = 0; c < n_cells; ++c) {
+      const unsigned first = F.grid_cells[c] >> 8, cnt = F.grid_cells[c] & 255u;
+      if ((size_t)first + cnt > F.grid_refs.size()) return fail(RRT_ERR_INVALID, "flatten check: grid cell run out of range");
+      for (unsigned k = 0; k < cnt; ++k) {
+        const int p = F.grid_refs[first + k];
+        if (p < 0 || p >= F.n_prims || in_front[p]) return fail(RRT_ERR_INVALID, "flatten check: grid reference out of range");
+      }
+    }
+    for (int p = 0; p < F.n_prims; ++p) {
+      if (in_front[p]) continue;
+      const float4 p0 = F.prims[4 * p], p1 = F.prims[4 * p + 1];
+      const float c[3] = {p0.x, p0.y, p0.z}, d[3] = {p1.x, p1.y, p1.z};
+      int c0[3], c1[3];
+      for (int a = 0; a < 3; ++a) {   // the sphere's swept box in cell coordinates, the f32 way the kernel computes them
+        const float lo = std::min(c[a], c[a] + d[a]) - std::fabs(p0.w), hi = std::max(c[a], c[a] + d[a]) + std::fabs(p0.w);
+        if (lo < F.glo[a] || hi > F.ghi[a]) return fail(RRT_ERR_INVALID, "flatten check: sphere outside the grid");
+        c0[a] = std::max(0, std::min(F.gres[a] - 1, (int)((lo - F.glo[a]) * F.ginv[a])));
+        c1[a] = std::max(0, std::min(F.gres[a] - 1, (int)((hi - F.glo[a]) * F.ginv[a])));
+      }
+      for (int z = c0[2]; z <= c1[2]; ++z) for (int y = c0[1]; y <= c1[1]; ++y) for (int x = c0[0]; x <= c1[0]; ++x) {
+        const unsigned h = F.grid_cells[((size_t)z * F.gres[1] + y) * F.gres[0] + x];
+        bool found = false;
+        for (unsigned k = 0; k < (h & 255u); ++k) found |= F.grid_refs[(h >> 8) + k] == p;
+        if (!found) return fail(RRT_ERR_INVALID, "flatten check: sphere missing from a grid cell it overlaps");
+      }
+    }
+  }
   if (n_prims) *n_prims = F.n_prims;
   if (n_nodes) *n_nodes = nn;
   if (bvh_depth) *bvh_depth = F.bvh_depth;

@@ -56,7 +56,7 @@ struct rrt_scene {
   rrt_ctx* ctx = nullptr;
   std::vector<void*> allocs;
   rrt::DevScene dev;
-  int n_nodes = 0, n_prims = 0, n_media = 0, n_lights = 0;
+  int n_nodes = 0, n_prims = 0, n_media = 0, n_lights = 0, n_grid_cells = 0;
   uint64_t h2d_bytes = 0;
   std::vector<rrt_scene*> parts;      // scene of a group context: one uploaded copy per member device
 };

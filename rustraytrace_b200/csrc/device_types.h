@@ -170,6 +170,17 @@ struct DevScene {
   int n_nodes, n_prims, n_media, n_lights;
   int has_motion;    // any sphere with dc != 0
   int features;      // SceneFeature bits
+  // Uniform grid over the tree's primitives (flatten.cpp build_grid), or grid_cells == null.  A sphere field
+  // (the book-1 final scene, the bouncing spheres of book 2) is many primitives of one size spread evenly:
+  // a ray leaving the ground has to descend ~9 levels of any BVH to learn that its neighbourhood is empty,
+  // where a grid reads the cell it stands in.  cells[(z ry + y) rx + x] = first reference << 8 | count;
+  // refs[] = flat sphere indices.  Built for sphere-only trees the flattener finds evenly filled; the BVH
+  // stays (the f64 probe walks it, RRT_NO_GRID=1 renders with it).
+  const unsigned* grid_cells;
+  const int* grid_refs;
+  float glo[3], ghi[3];     // bounds of the grid
+  float gcell[3], ginv[3];  // cell size and its reciprocal per axis
+  int gres[3];
 };
 
 // One launch's share of the frame.
@@ -185,6 +196,7 @@ struct DevWork {
   int max_depth;
   int spp_eff;
   unsigned seed_lo, seed_hi;
+  unsigned rkeys[20];   // Philox round keys of the seed (rng.cuh philox_round_keys; 2 per round, up to 10 rounds)
   int atomic_accum;     // chunks > 1: accumulate with red.add
   int compact;          // tile sharding for a gather: accum holds this rank's super tiles back to back
                         //   (1024 float4 each, row-major inside the tile) instead of a full frame

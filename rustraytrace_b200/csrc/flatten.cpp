@@ -588,6 +588,80 @@ bool tex_needs_ok(const rrt_scene_desc* d, int t, int depth) {
   return x.kind == RRT_T_SOLID;
 }
 
+// Uniform grid over the tree's items (device_types.h DevScene::grid_cells).  Only for trees of spheres that
+// fill it evenly: resolution from the item density (RRT_GRID_LAMBDA cells per item), every sphere referenced
+// from each cell its (padded) swept box overlaps.  Accepted when the result is balanced — few references per
+// sphere, no crowded cell — because that is when "read the cell you stand in" beats "descend the hierarchy":
+// measured on the book-1 final scene, C2 +15-18 % (profiles/README.md r02k).  RRT_NO_GRID=1 keeps the BVH,
+// RRT_FORCE_GRID=1 skips the balance test, RRT_GRID_LAMBDA=x overrides the density.
+#ifndef RRT_GRID_LAMBDA
+#define RRT_GRID_LAMBDA 0.5
+#endif
+#ifndef RRT_GRID_MIN_ITEMS
+#define RRT_GRID_MIN_ITEMS 64
+#endif
+void build_grid(const std::vector<BakedPrim>& items, const std::vector<int>& item_flat, FlatScene& out) {
+  out.grid_cells.clear(); out.grid_refs.clear();
+  for (int a = 0; a < 3; ++a) out.gres[a] = 0;
+  if (std::getenv("RRT_NO_GRID")) return;
+  const bool force = std::getenv("RRT_FORCE_GRID") != nullptr;
+  if (items.empty() || (items.size() < (size_t)RRT_GRID_MIN_ITEMS && !force)) return;
+  double lo[3], hi[3], mean_ext[3] = {0, 0, 0};
+  for (int a = 0; a < 3; ++a) { lo[a] = std::numeric_limits<double>::infinity(); hi[a] = -lo[a]; }
+  for (size_t i = 0; i < items.size(); ++i) {
+    if (items[i].kind != PRIM_SPHERE || item_flat[i] < 0) return;   // spheres only
+    for (int a = 0; a < 3; ++a) {
+      lo[a] = std::min(lo[a], items[i].lo[a]); hi[a] = std::max(hi[a], items[i].hi[a]);
+      mean_ext[a] += (items[i].hi[a] - items[i].lo[a]) / (double)items.size();
+    }
+  }
+  const char* le = std::getenv("RRT_GRID_LAMBDA");
+  const double lambda = le ? std::atof(le) : RRT_GRID_LAMBDA;
+  // a flat field is one cell thick: an axis no longer than the items themselves gets the items' extent
+  double ext[3], vol = 1;
+  for (int a = 0; a < 3; ++a) { ext[a] = std::max(hi[a] - lo[a], std::max(mean_ext[a], 1e-9)); vol *= ext[a]; }
+  const double dens = std::cbrt(lambda * (double)items.size() / vol);
+  int res[3];
+  double cell[3];
+  for (int a = 0; a < 3; ++a) {
+    res[a] = std::max(1, std::min(128, (int)std::lround(ext[a] * dens)));
+    const double pad = 1e-3 * ext[a] / res[a] + 1e-6 * std::max(std::fabs(lo[a]), std::fabs(hi[a]));   // the bounds, outwards
+    lo[a] -= pad; hi[a] += pad;
+    cell[a] = (hi[a] - lo[a]) / res[a];
+  }
+  const size_t n_cells = (size_t)res[0] * res[1] * res[2];
+  std::vector<std::vector<int>> lists(n_cells);
+  size_t n_refs = 0;
+  for (size_t i = 0; i < items.size(); ++i) {
+    int c0[3], c1[3];
+    for (int a = 0; a < 3; ++a) {
+      // padded by a thousandth of a cell: the f32 walk may leave a cell that far from where f64 would
+      const double pad = 1e-3 * cell[a] + 4e-7 * std::max(std::fabs(items[i].lo[a]), std::fabs(items[i].hi[a]));
+      c0[a] = std::max(0, std::min(res[a] - 1, (int)std::floor((items[i].lo[a] - pad - lo[a]) / cell[a])));
+      c1[a] = std::max(0, std::min(res[a] - 1, (int)std::floor((items[i].hi[a] + pad - lo[a]) / cell[a])));
+    }
+    for (int z = c0[2]; z <= c1[2]; ++z)
+      for (int y = c0[1]; y <= c1[1]; ++y)
+        for (int x = c0[0]; x <= c1[0]; ++x) { lists[((size_t)z * res[1] + y) * res[0] + x].push_back(item_flat[i]); ++n_refs; }
+  }
+  size_t crowded = 0;
+  for (const std::vector<int>& l : lists) crowded = std::max(crowded, l.size());
+  if (crowded > 255 || n_refs >= (1u << 24)) return;
+  if (!force && ((double)n_refs > 4.0 * (double)items.size() || crowded > 12)) return;   // not an even field
+  out.grid_cells.resize(n_cells);
+  out.grid_refs.reserve(n_refs + 1);
+  for (size_t c = 0; c < n_cells; ++c) {
+    out.grid_cells[c] = ((unsigned)out.grid_refs.size() << 8) | (unsigned)lists[c].size();
+    for (int r : lists[c]) out.grid_refs.push_back(r);
+  }
+  if (out.grid_refs.empty()) out.grid_refs.push_back(0);
+  for (int a = 0; a < 3; ++a) {
+    out.glo[a] = (float)lo[a]; out.ghi[a] = (float)hi[a];
+    out.gcell[a] = (float)((hi[a] - lo[a]) / res[a]); out.ginv[a] = (float)(res[a] / (hi[a] - lo[a]));
+    out.gres[a] = res[a];
+  }
+}
+
 }  // namespace
 
 int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, int single_leaf_max, int max_leaf) {
@@ -800,6 +874,7 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
   out.bvh_depth = B.max_depth_seen;
   // leaf -> contiguous prim run (spheres first, then quads); prims emitted in `order` sequence
   std::vector<int> leaf_ref(B.nodes.size(), 0);
+  std::vector<int> item_flat(items.size(), -1);   // tree item -> flat primitive index (box groups: -1)
   {
     // emit prims leaf by leaf in B.order sequence (DFS), reordering within the leaf by kind
     int emitted = 0;
@@ -839,7 +914,7 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
         // `contains`), so a leaf that tests them in that order with `t <= closest` needs no tie lookup
         // (quad_pairs_hit32 relies on it; quad_hit32's explicit rule agrees with it)
         if (pass == 1) std::stable_sort(run.begin(), run.end(), [&](int a, int b) { return items[a].order < items[b].order; });
-        for (int i : run) { emit_prim32(items[i], out.prims); emit_prim64(items[i], out.prims64); (pass == 0 ? s : q)++; }
+        for (int i : run) { item_flat[i] = (int)(out.prims.size() / 4); emit_prim32(items[i], out.prims); emit_prim64(items[i], out.prims64); (pass == 0 ? s : q)++; }
       }
       leaf_ref[li] = make_leaf_ref(emitted, s, q);
       emitted += n.count;
@@ -891,6 +966,7 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
     out.nodes.push_back(i4(ref0, ref1, 0, 0));
   }
   out.root_ref = 0;
+  build_grid(items, item_flat, out);
 #ifdef RRT_BVH4
   // Experiment (profiles/README.md, r02): the binary tree collapsed to 4-wide nodes — a node's children
   // are its grandchildren (a leaf child stays one child) — so that a traversal step tests four boxes with

@@ -258,6 +258,49 @@ __device__ __forceinline__ void leaf1_hit32(const float4* __restrict__ prims, co
   else quad_hit32(prims, leaf >> 8, r, tmin, skip, h);
 }
 
+// The uniform grid of a sphere field (device_types.h DevScene::grid_cells, flatten.cpp build_grid): clip the ray
+// to the grid, then walk the cells it crosses front to back (Amanatides & Woo) and test the spheres each
+// cell references, until the next cell begins behind the closest hit.  A sphere referenced by several
+// cells is tested in each — sphere_hit32's result does not depend on order or repetition, so the hit and
+// the equal-t rule are those of the tree walk.
+__device__ __forceinline__ void grid_hit32(const DevScene& S, const Ray32& r, float a, float inv_a, float tmin, int skip,
+                                           bool motion, Hit32& h) {
+  const float idx = safe_rcp(r.d.x), idy = safe_rcp(r.d.y), idz = safe_rcp(r.d.z);
+  const float x0 = (S.glo[0] - r.o.x) * idx, x1 = (S.ghi[0] - r.o.x) * idx;
+  const float y0 = (S.glo[1] - r.o.y) * idy, y1 = (S.ghi[1] - r.o.y) * idy;
+  const float z0 = (S.glo[2] - r.o.z) * idz, z1 = (S.ghi[2] - r.o.z) * idz;
+  const float t0 = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
+  const float t1 = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), h.t));
+  if (!(t0 <= t1)) return;
+  const int rx = S.gres[0], ry = S.gres[1], rz = S.gres[2];
+  int ix = min(max((int)((fmaf(t0, r.d.x, r.o.x) - S.glo[0]) * S.ginv[0]), 0), rx - 1);
+  int iy = min(max((int)((fmaf(t0, r.d.y, r.o.y) - S.glo[1]) * S.ginv[1]), 0), ry - 1);
+  int iz = min(max((int)((fmaf(t0, r.d.z, r.o.z) - S.glo[2]) * S.ginv[2]), 0), rz - 1);
+  const bool px = r.d.x >= 0.0f, py = r.d.y >= 0.0f, pz = r.d.z >= 0.0f;
+  // parameter at which the ray leaves the current cell along each axis, and its increment per cell
+  float tmx = (fmaf((float)(ix + (px ? 1 : 0)), S.gcell[0], S.glo[0]) - r.o.x) * idx;
+  float tmy = (fmaf((float)(iy + (py ? 1 : 0)), S.gcell[1], S.glo[1]) - r.o.y) * idy;
+  float tmz = (fmaf((float)(iz + (pz ? 1 : 0)), S.gcell[2], S.glo[2]) - r.o.z) * idz;
+  const float tdx = S.gcell[0] * fabsf(idx), tdy = S.gcell[1] * fabsf(idy), tdz = S.gcell[2] * fabsf(idz);
+  const int sx = px ? 1 : -1, sy = py ? rx : -rx, sz = pz ? rx * ry : -(rx * ry);
+  // cells still to cross along each axis before the ray leaves the grid
+  int nx = px ? rx - 1 - ix : ix, ny = py ? ry - 1 - iy : iy, nz = pz ? rz - 1 - iz : iz;
+  int cell = (iz * ry + iy) * rx + ix;
+  for (;;) {
+    const unsigned hdr = __ldg(S.grid_cells + cell);
+    const int* refs = S.grid_refs + (hdr >> 8);
+    const int cnt = (int)(hdr & 255u);
+    for (int k = 0; k < cnt; ++k) sphere_hit32(S.prims, __ldg(refs + k), r, a, inv_a, tmin, skip, motion, h);
+    const bool bx = tmx <= tmy && tmx <= tmz, by = !bx && tmy <= tmz;
+    const float tn = bx ? tmx : (by ? tmy : tmz);
+    int left;
+    if (bx) { left = nx--; tmx += tdx; cell += sx; }
+    else if (by) { left = ny--; tmy += tdy; cell += sy; }
+    else { left = nz--; tmz += tdz; cell += sz; }
+    if (left <= 0 || tn > fminf(t1, h.t)) break;
+  }
+}
+
 // World::hit for the render kernel: closest hit in (tmin, +inf).
 // Nodes and primitives come through L1 (ld.global.nc).
 template <int FEAT>
@@ -272,6 +315,7 @@ __device__ inline void world_hit32(const DevScene& S, const Ray32& r, float tmin
   }
   // front run (flatten.cpp): primitives spanning most of the scene, tested by all lanes together
   if (S.front_ref != -1) leaf_hit32<FEAT>(S.prims, S.boxes, ~S.front_ref, r, V3f(0.0f, 0.0f, 0.0f), a, inv_a, tmin, skip, motion, h);
+  if (S.grid_cells) { grid_hit32(S, r, a, inv_a, tmin, skip, motion, h); return; }   // an even sphere field: cells instead of the tree
   const float idx = safe_rcp(r.d.x), idy = safe_rcp(r.d.y), idz = safe_rcp(r.d.z);
   float oodx = r.o.x * idx, oody = r.o.y * idy, oodz = r.o.z * idz;
   asm("" : "+f"(oodx), "+f"(oody), "+f"(oodz));  // opaque: keep in registers, do not rematerialise in the loop

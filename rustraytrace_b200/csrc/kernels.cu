@@ -92,7 +92,9 @@ __global__ void kat_rng_kernel(unsigned k0, unsigned k1, unsigned pixel, unsigne
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   PathRng rng;
-  rng.pixel = pixel; rng.sample = sample0 + (unsigned)i; rng.k0 = k0; rng.k1 = k1;
+  uint32_t rk[2 * RRT_PHILOX_ROUNDS];
+  philox_round_keys(k0, k1, rk, RRT_PHILOX_ROUNDS);
+  rng.pixel = pixel; rng.sample = sample0 + (unsigned)i; rng.rk = rk;
   if (raw4) philox4x32<RRT_PHILOX_ROUNDS>(rng.pixel, rng.sample, bounce, block, k0, k1, raw4 + 4 * (size_t)i);
   if (u5) {
     const Rand4 r = rng.draw(bounce, block);

@@ -144,7 +144,7 @@ int rrt::multi_scene_create(rrt_ctx* g, const FlatScene& F, rrt_scene** out) {
     sc->parts.push_back(part);
     sc->h2d_bytes += part->h2d_bytes;
   }
-  sc->n_nodes = sc->parts[0]->n_nodes; sc->n_prims = sc->parts[0]->n_prims;
+  sc->n_nodes = sc->parts[0]->n_nodes; sc->n_prims = sc->parts[0]->n_prims; sc->n_grid_cells = sc->parts[0]->n_grid_cells;
   sc->n_media = sc->parts[0]->n_media; sc->n_lights = sc->parts[0]->n_lights;
   g->scenes.push_back(sc);
   *out = sc;

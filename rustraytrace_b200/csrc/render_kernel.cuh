@@ -338,7 +338,7 @@ render_kernel(const __grid_constant__ RenderArgs A) {
     PathRng rng;
     rng.pixel = (uint32_t)(py * W.width + px);
     rng.sample = 0;
-    rng.k0 = W.seed_lo; rng.k1 = W.seed_hi;
+    rng.rk = W.rkeys;
 
     V3f sum(0.0f, 0.0f, 0.0f);
     // Sample stealing inside the warp: a lane that has traced all samples of its own pixel goes on

@@ -98,7 +98,7 @@ render_kernel_pool(const __grid_constant__ RenderArgs A) {
     const int n_total = n_valid * (s1 - s0);
     int issued = 0;
     PathRng rng;
-    rng.k0 = W.seed_lo; rng.k1 = W.seed_hi;
+    rng.rk = W.rkeys;
 
     for (;;) {
       // ---- regenerate: the dead slots, compacted ---------------------------------------------------------

@@ -30,7 +30,7 @@ def main():
         print(json.dumps(dict(config=name, w=s.width, h=s.height, spp=st["spp_effective"], paths=st["paths"],
                               kernel_ms=round(st["kernel_ms"], 3), mpaths_s=round(st["paths"] / st["kernel_ms"] / 1e3, 1),
                               mean=[round(float(x), 5) for x in (a[..., :3].sum(axis=(0, 1)) / a[..., 3].sum())],
-                              nodes=st["n_bvh_nodes"], prims=st["n_prims"], sm=st["sm_count"])), flush=True)
+                              nodes=st["n_bvh_nodes"], grid=st["n_grid_cells"], prims=st["n_prims"], sm=st["sm_count"])), flush=True)
 
 
 if __name__ == "__main__":

@@ -1,0 +1,140 @@
+"""The uniform grid of sphere fields (flatten.cpp build_grid, intersect.cuh grid_hit32).
+
+An even field of spheres — the book-1 final scene (in_one_weekend/mod.rs:65-108), the bouncing spheres
+of book 2 (the_next_week/mod.rs:96-149) — is walked cell by cell instead of through the BVH.  The grid
+only changes WHERE the candidates come from: every sphere test is sphere_hit32's, so hits, equal-t
+decisions and therefore whole frames must be those of the tree walk, bit for bit.
+
+CPU tier: which scenes get a grid, and the flattener's own check of the cell tables (every sphere
+referenced from every cell its swept box overlaps).  GPU tier: f32 probe and deterministic renders with
+and without the grid are identical; forced grids over uneven random sphere scenes as well.
+"""
+import numpy as np
+import pytest
+
+import rustraytrace_b200 as R
+
+F = R._ffi
+
+
+def random_spheres(seed, n, moving=False, spread=6.0):
+    rng = np.random.default_rng(seed)
+    b = R.DescBuilder()
+    mats = [b.lambertian(tuple(rng.uniform(0.2, 0.9, 3))) for _ in range(3)]
+    mats.append(b.material(F.M_METAL, albedo=(0.8, 0.8, 0.8), fuzz=0.1))
+    mats.append(b.material(F.M_DIELECTRIC, ri=1.5))
+    items = []
+    for _ in range(n):
+        c = tuple(rng.uniform(-spread, spread, 3) * np.array([1.0, 0.25, 1.0]))
+        r = float(rng.choice([0.1, 0.2, 0.2, 0.3, 0.9]))
+        m = mats[rng.integers(len(mats))]
+        if moving and rng.random() < 0.5:
+            c1 = tuple(np.array(c) + rng.uniform(-0.5, 0.5, 3))
+            items.append(b.sphere(c, r, m, center2=c1))
+        else:
+            items.append(b.sphere(c, r, m))
+    world = b.bvh(items) if seed % 2 else b.list(items)
+    cam = R.make_camera(image_width=128, aspect_ratio=1.0, samples_per_pixel=16, max_depth=8, background=(0.6, 0.7, 0.9),
+                        vfov=50.0, lookfrom=(float(rng.uniform(-3, 3)), float(rng.uniform(1.0, 4.0)), 11.0), lookat=(0.0, 0.0, 0.0))
+    return b.desc(world), cam
+
+
+# ---- CPU tier --------------------------------------------------------------------------------------
+def test_grid_is_laid_over_even_sphere_fields_only(monkeypatch):
+    for book, no, want in [("in_one_weekend", None, True), ("in_one_weekend_gpu", None, True), ("the_next_week", 1, True),
+                           ("the_next_week", 2, False), ("the_next_week", 7, False), ("the_next_week", 9, False),
+                           ("the_rest_of_your_life", None, False)]:
+        s = R.BookScene(book, no, overrides=dict(image_width=64))
+        g = R.flatten_grid(s.desc)
+        assert (g["res"] != (0, 0, 0)) == want, (book, no, g)
+        if want:
+            n = R.flatten_check(s.desc)["n_prims"]       # the check walks the cell tables too
+            assert g["res"][1] == 1                      # a field on the ground: one cell thick
+            assert g["n_refs"] <= 4 * n and g["max_per_cell"] <= 12
+    s = R.BookScene("in_one_weekend", None, overrides=dict(image_width=64))
+    monkeypatch.setenv("RRT_NO_GRID", "1")
+    assert R.flatten_grid(s.desc)["res"] == (0, 0, 0)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_forced_grid_passes_the_flattener_check(seed, monkeypatch):
+    """Uneven fields (radii 0.1-0.9, clumps, moving spheres): not what the balance test accepts, but a forced
+    grid must still reference every sphere from every cell its swept box touches."""
+    d, _ = random_spheres(seed, 40 + 60 * seed, moving=bool(seed & 1))
+    monkeypatch.setenv("RRT_FORCE_GRID", "1")
+    g = R.flatten_grid(d)
+    assert g["res"] != (0, 0, 0) and g["n_refs"] >= 40 + 60 * seed
+    R.flatten_check(d)
+
+
+def test_small_or_mixed_trees_keep_the_bvh():
+    d, _ = random_spheres(1, 20)
+    assert R.flatten_grid(d)["res"] == (0, 0, 0)        # under RRT_GRID_MIN_ITEMS
+    b = R.DescBuilder()
+    m = b.lambertian((0.5, 0.5, 0.5))
+    items = [b.sphere((float(x), 0.2, float(z)), 0.2, m) for x in range(-6, 6) for z in range(-6, 6)]
+    assert R.flatten_grid(b.desc(b.list(items)))["res"][1] == 1
+    items.append(b.quad((-1.0, 0.5, -1.0), (2.0, 0.0, 0.0), (0.0, 0.0, 2.0), m))   # one quad in the tree: no grid
+    assert R.flatten_grid(b.desc(b.list(items)))["res"] == (0, 0, 0)
+
+
+# ---- GPU tier --------------------------------------------------------------------------------------
+def _both(desc, cam, integrator, monkeypatch, force=False):
+    """(probe ids, probe t, deterministic frame) with the grid and with RRT_NO_GRID."""
+    monkeypatch.setenv("RRT_DETERMINISTIC", "1")
+    ctx = R.Context(0)
+    monkeypatch.delenv("RRT_DETERMINISTIC")
+    out = []
+    for grid in (True, False):
+        if not grid:
+            monkeypatch.setenv("RRT_NO_GRID", "1")
+        elif force:
+            monkeypatch.setenv("RRT_FORCE_GRID", "1")
+        gs = ctx.scene(desc)
+        monkeypatch.delenv("RRT_NO_GRID", raising=False)
+        monkeypatch.delenv("RRT_FORCE_GRID", raising=False)
+        ids, t = ctx.probe(gs, cam, 32)
+        frame = ctx.render(gs, cam, integrator, seed=5)
+        cells = ctx.stats()["n_grid_cells"]
+        assert (cells > 0) == grid
+        out.append((ids, t, frame))
+        gs.close()
+    ctx.close()
+    return out
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("book,scene_no", [("in_one_weekend", None), ("in_one_weekend_gpu", None), ("the_next_week", 1)])
+def test_grid_and_tree_render_the_same_frame_bit_for_bit(book, scene_no, monkeypatch):
+    s = R.BookScene(book, scene_no, overrides=dict(image_width=200, samples_per_pixel=24, max_depth=16))
+    (ids, t, a), (pids, pt, b) = _both(s.desc, s.camera, s.integrator, monkeypatch)
+    assert np.array_equal(ids, pids) and np.array_equal(t, pt)
+    assert np.array_equal(a, b)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed", range(6))
+def test_forced_grid_over_uneven_spheres_matches_the_tree(seed, monkeypatch):
+    d, cam = random_spheres(seed, 40 + 60 * seed, moving=bool(seed & 1))
+    integ = F.INT_BOOK2 if seed & 1 else F.INT_BOOK1
+    (ids, t, a), (pids, pt, b) = _both(d, cam, integ, monkeypatch, force=True)
+    assert (ids >= 0).any()
+    assert np.array_equal(ids, pids) and np.array_equal(t, pt)
+    assert np.array_equal(a, b)
+
+
+@pytest.mark.gpu
+def test_grid_probe_against_the_oracle():
+    """The grid walk in the f32 probe against the oracle's f64 pointer tree: ids equal except on silhouettes."""
+    import oracle_ffi as O
+    s = R.BookScene("in_one_weekend", None, overrides=dict(image_width=400))
+    ctx = R.Context(0)
+    gs = ctx.scene(s.desc)
+    assert ctx.stats()["n_grid_cells"] > 0
+    ids, t = ctx.probe(gs, s.camera, 32)
+    oids, ot = O.OracleScene(s.desc).probe(s.camera)
+    gs.close(); ctx.close()
+    assert (ids != oids).mean() <= 2e-5
+    hit = (oids >= 0) & (ids == oids)
+    rel = np.abs(t[hit] - ot[hit]) / ot[hit]
+    assert np.percentile(rel, 99) <= 1e-4
