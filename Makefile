@@ -27,11 +27,14 @@ $(CSRC)/api.o: $(CSRC)/api.cu $(CSRC)/*.cuh $(CSRC)/*.h $(CSRC)/flatten.hpp incl
 # several GPUs behind the C ABI: NCCL reduce / gather of the frame (links libnccl)
 $(CSRC)/multi.o: $(CSRC)/multi.cu $(CSRC)/*.h $(CSRC)/flatten.hpp include/rrt.h
 	$(NVCC) $(NVFLAGS) -c $< -o $@
+# rrt_probe_static: the probe with its scratch in a static device array (no cudaMalloc)
+$(CSRC)/noalloc.o: $(CSRC)/noalloc.cu $(CSRC)/*.h $(CSRC)/flatten.hpp include/rrt.h
+	$(NVCC) $(NVFLAGS) -c $< -o $@
 $(CSRC)/flatten.o: $(CSRC)/flatten.cpp $(CSRC)/flatten.hpp $(CSRC)/device_types.h include/rrt.h
 	$(NVCC) $(NVFLAGS) -x cu -c $< -o $@
 
 KOBJ := $(CSRC)/kernels_book1.o $(CSRC)/kernels_book2.o $(CSRC)/kernels_book3.o
-$(PKG)/librrt.so: $(CSRC)/kernels.o $(KOBJ) $(CSRC)/probe64.o $(CSRC)/api.o $(CSRC)/multi.o $(CSRC)/flatten.o
+$(PKG)/librrt.so: $(CSRC)/kernels.o $(KOBJ) $(CSRC)/probe64.o $(CSRC)/api.o $(CSRC)/multi.o $(CSRC)/noalloc.o $(CSRC)/flatten.o
 	$(NVCC) -gencode arch=compute_100a,code=sm_100a -shared -o $@ $^ -cudart shared -lnccl
 
 HOST_SRC := $(HOST)/books.cpp $(HOST)/rtw_image.cpp $(HOST)/jpeg_decode.cpp $(HOST)/render_io.cpp

@@ -51,6 +51,7 @@ extern "C" {
     pub fn rrt_render(ctx: *mut RrtCtx, scene: *const RrtScene, cam: *const RrtCamera, p: *const RrtRenderParams, accum_host: *mut f32) -> c_int;
     pub fn rrt_render_frame(ctx: *mut RrtCtx, desc: *const RrtSceneDesc, cam: *const RrtCamera, p: *const RrtRenderParams, accum_host: *mut f32) -> c_int;
     pub fn rrt_probe(ctx: *mut RrtCtx, scene: *const RrtScene, cam: *const RrtCamera, precision: c_int, prim_id: *mut i32, t: *mut f64) -> c_int;
+    pub fn rrt_probe_static(ctx: *mut RrtCtx, scene: *const RrtScene, cam: *const RrtCamera, precision: c_int, prim_id: *mut i32, t: *mut f64) -> c_int;
     pub fn rrt_resolve_rgb8(ctx: *mut RrtCtx, accum_host: *const f32, w: c_int, h: c_int, spp: c_int, rgb: *mut u8) -> c_int;
     pub fn rrt_render_device(ctx: *mut RrtCtx, scene: *const RrtScene, cam: *const RrtCamera, p: *const RrtRenderParams, accum_dev: *mut f32) -> c_int;
     pub fn rrt_resolve_rgb8_device(ctx: *mut RrtCtx, accum_dev: *const f32, w: c_int, h: c_int, spp: c_int, rgb_dev: *mut u8) -> c_int;

@@ -276,6 +276,20 @@ int rrt_render_frame(rrt_ctx* ctx, const rrt_scene_desc* desc, const rrt_camera*
 int rrt_probe(rrt_ctx* ctx, const rrt_scene* scene, const rrt_camera* cam, int precision,
               int32_t* prim_id, double* t);
 
+/* rrt_probe without any allocation (csrc/noalloc.cu).  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  Same arguments, same results as rrt_probe; the device
+ * staging of the per-pixel outputs (12 bytes a pixel) is a static device array of
+ * RRT_PROBE_STATIC_MAX_PIXELS pixels = 12 MiB, which every GPU that loads the library holds until exit.
+ * A frame with more pixels is refused with RRT_ERR_UNSUPPORTED (use rrt_probe).  The call makes no
+ * cudaMalloc / cudaFree; the first call on a device looks the array's address up (cudaGetSymbolAddress).
+ * All calls on a device share the array and it keeps the last call's contents (every pixel of the frame
+ * is written before it is read back, so nothing needs clearing): calls that overlap on one GPU race —
+ * serialise them. */
+#define RRT_PROBE_STATIC_MAX_PIXELS 1048576
+int rrt_probe_static(rrt_ctx* ctx, const rrt_scene* scene, const rrt_camera* cam, int precision,
+                     int32_t* prim_id, double* t);
+
 /* write_ppm_from_accum's per-pixel arithmetic (src/render_io.rs:8-26) on the device:
  * accum (device, RGBA f32) -> rgb8 (device, W*H*3).  spp<=0 uses accum.w per pixel. */
 int rrt_resolve_rgb8_device(rrt_ctx* ctx, const float* accum_dev, int width, int height, int spp,

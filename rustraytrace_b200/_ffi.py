@@ -93,6 +93,7 @@ O_BITS = {"aspect_ratio": 1 << 0, "image_width": 1 << 1, "samples_per_pixel": 1 
 
 # every symbol the two headers declare: (name, restype, argtypes)
 VP = C.c_void_p
+PROBE_STATIC_MAX_PIXELS = 1048576  # RRT_PROBE_STATIC_MAX_PIXELS (include/rrt.h)
 RRT_SYMBOLS = [
     ("rrt_init", c_int, [c_int, C.POINTER(VP)]),
     ("rrt_shutdown", None, [VP]),
@@ -109,6 +110,7 @@ RRT_SYMBOLS = [
     ("rrt_render_device", c_int, [VP, VP, C.POINTER(Camera), C.POINTER(RenderParams), VP]),
     ("rrt_render_frame", c_int, [VP, C.POINTER(SceneDesc), C.POINTER(Camera), C.POINTER(RenderParams), VP]),
     ("rrt_probe", c_int, [VP, VP, C.POINTER(Camera), c_int, VP, VP]),
+    ("rrt_probe_static", c_int, [VP, VP, C.POINTER(Camera), c_int, VP, VP]),
     ("rrt_resolve_rgb8_device", c_int, [VP, VP, c_int, c_int, c_int, VP]),
     ("rrt_resolve_rgb8", c_int, [VP, VP, c_int, c_int, c_int, VP]),
     ("rrt_get_stats", c_int, [VP, C.POINTER(Stats)]),

@@ -351,6 +351,14 @@ class Context:
         _check(F.rrt().rrt_probe(self._h, gscene._handle, C.byref(camera), int(precision), ids.ctypes.data, t.ctypes.data))
         return ids, t
 
+    def probe_static(self, gscene, camera, precision=64):
+        """rrt_probe_static: the probe without any device allocation (static scratch, <= F.PROBE_STATIC_MAX_PIXELS pixels)."""
+        H = F.rrt().rrt_image_height(C.byref(camera))
+        ids = np.empty((H, camera.image_width), dtype=np.int32)
+        t = np.empty((H, camera.image_width), dtype=np.float64)
+        _check(F.rrt().rrt_probe_static(self._h, gscene._handle, C.byref(camera), int(precision), ids.ctypes.data, t.ctypes.data))
+        return ids, t
+
     def resolve(self, accum, spp):
         a = np.ascontiguousarray(accum, dtype=np.float32)
         H, W = a.shape[0], a.shape[1]

@@ -14,8 +14,9 @@ for b in 1 2 3; do nvcc $F --use_fast_math "$@" -c $C/kernels_book$b.cu -o $tmp/
 nvcc $F -fmad=false "$@" -c $C/probe64.cu -o $tmp/probe64.o &
 nvcc $F --use_fast_math "$@" -c $C/api.cu -o $tmp/api.o &
 nvcc $F --use_fast_math "$@" -c $C/multi.cu -o $tmp/multi.o &
+nvcc $F --use_fast_math "$@" -c $C/noalloc.cu -o $tmp/noalloc.o &
 nvcc $F --use_fast_math "$@" -x cu -c $C/flatten.cpp -o $tmp/flatten.o &
 wait
-nvcc -gencode arch=compute_100a,code=sm_100a -shared -o $out/librrt_$name.so $tmp/kernels.o $tmp/kernels_book1.o $tmp/kernels_book2.o $tmp/kernels_book3.o $tmp/probe64.o $tmp/api.o $tmp/multi.o $tmp/flatten.o -cudart shared -lnccl
+nvcc -gencode arch=compute_100a,code=sm_100a -shared -o $out/librrt_$name.so $tmp/kernels.o $tmp/kernels_book1.o $tmp/kernels_book2.o $tmp/kernels_book3.o $tmp/probe64.o $tmp/api.o $tmp/multi.o $tmp/noalloc.o $tmp/flatten.o -cudart shared -lnccl
 rm -rf $tmp
 echo built $out/librrt_$name.so
