@@ -316,9 +316,11 @@ int rrt_shard_plan(const rrt_camera* cam, const rrt_render_params* params, int32
 int rrt_flatten_check(const rrt_scene_desc* desc, int32_t* n_prims, int32_t* n_nodes, int32_t* bvh_depth,
                       int32_t* n_media, int32_t* n_lights);
 int rrt_scene_features(const rrt_scene_desc* desc, int32_t* features);
-/*   rrt_flatten_grid: the uniform grid the flattener lays over an even field of spheres (rrt_stats.n_grid_cells):
- *   cells per axis (0, 0, 0: the scene is walked through its BVH), references in all cells, most in one cell. */
-int rrt_flatten_grid(const rrt_scene_desc* desc, int32_t res3[3], int32_t* n_refs, int32_t* max_per_cell);
+/*   rrt_flatten_grid: the uniform grid the flattener lays over an even field of equal spheres (kind 0) or
+ *   axis-aligned boxes (kind 1) (rrt_stats.n_grid_cells): cells per axis (0, 0, 0: no such grid — without any grid
+ *   the scene is walked through its BVH), items in it, references in all cells, most in one cell. */
+int rrt_flatten_grid(const rrt_scene_desc* desc, int kind, int32_t res3[3], int32_t* n_items, int32_t* n_refs,
+                     int32_t* max_per_cell);
 void rrt_philox_kat(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1,
                     uint32_t* out4);
 /*   rrt_philox_kat_rounds: the same block at 7 or 10 rounds (Random123 publishes known answers for both);

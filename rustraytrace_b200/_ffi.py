@@ -118,7 +118,7 @@ RRT_SYMBOLS = [
                                C.POINTER(c_int), C.POINTER(c_dbl), VP]),
     ("rrt_flatten_check", c_int, [C.POINTER(SceneDesc)] + [C.POINTER(c_int)] * 5),
     ("rrt_scene_features", c_int, [C.POINTER(SceneDesc), C.POINTER(c_int)]),
-    ("rrt_flatten_grid", c_int, [C.POINTER(SceneDesc), C.POINTER(c_int * 3), C.POINTER(c_int), C.POINTER(c_int)]),
+    ("rrt_flatten_grid", c_int, [C.POINTER(SceneDesc), c_int, C.POINTER(c_int * 3), C.POINTER(c_int), C.POINTER(c_int), C.POINTER(c_int)]),
     ("rrt_philox_kat", None, [C.c_uint32] * 6 + [C.POINTER(C.c_uint32)]),
     ("rrt_philox_kat_rounds", c_int, [c_int] + [C.c_uint32] * 6 + [C.POINTER(C.c_uint32)]),
     ("rrt_philox_rounds", c_int, []),

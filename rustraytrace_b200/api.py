@@ -201,11 +201,12 @@ def flatten_check(desc):
     return dict(zip(("n_prims", "n_nodes", "bvh_depth", "n_media", "n_lights"), [x.value for x in v]))
 
 
-def flatten_grid(desc):
-    """Host-only: the uniform grid the flattener chose for the scene's sphere field (res (0, 0, 0): none, the BVH is walked)."""
-    res, n_refs, most = (F.c_int * 3)(), F.c_int(), F.c_int()
-    _check(F.rrt().rrt_flatten_grid(C.byref(desc), C.byref(res), C.byref(n_refs), C.byref(most)))
-    return dict(res=tuple(res), n_refs=n_refs.value, max_per_cell=most.value)
+def flatten_grid(desc, kind=0):
+    """Host-only: the uniform grid the flattener chose for the scene's field of spheres (kind 0) or boxes (kind 1);
+    res (0, 0, 0): none."""
+    res, n_items, n_refs, most = (F.c_int * 3)(), F.c_int(), F.c_int(), F.c_int()
+    _check(F.rrt().rrt_flatten_grid(C.byref(desc), int(kind), C.byref(res), C.byref(n_items), C.byref(n_refs), C.byref(most)))
+    return dict(res=tuple(res), n_items=n_items.value, n_refs=n_refs.value, max_per_cell=most.value)
 
 
 def scene_features(desc):

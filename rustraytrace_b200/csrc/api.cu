@@ -88,7 +88,8 @@ int rrt::scene_upload(rrt_ctx* c, const FlatScene& F, rrt_scene** out) {
   D.n_lights = (int)F.lights.size();
   D.has_motion = F.has_motion;
   D.features = F.features;
-  for (int a = 0; a < 3; ++a) { D.glo[a] = F.glo[a]; D.ghi[a] = F.ghi[a]; D.gcell[a] = F.gcell[a]; D.ginv[a] = F.ginv[a]; D.gres[a] = F.gres[a]; }
+  D.n_grids = 0;
+  for (size_t g = 0; g < F.grids.size() && g < RRT_MAX_GRIDS; ++g) { D.grids[g] = F.grids[g]; D.n_grids += F.grids[g].n_items > 0; }
   sc->n_nodes = D.n_nodes; sc->n_prims = D.n_prims; sc->n_media = D.n_media; sc->n_lights = D.n_lights;
   sc->n_grid_cells = (int)F.grid_cells.size();
   cudaError_t e = cudaStreamSynchronize(c->stream);  // the host vectors die when the caller returns
@@ -635,16 +636,23 @@ extern "C" int rrt_scene_features(const rrt_scene_desc* desc, int32_t* features)
   return RRT_OK;
 }
 
-extern "C" int rrt_flatten_grid(const rrt_scene_desc* desc, int32_t res3[3], int32_t* n_refs, int32_t* max_per_cell) {
+extern "C" int rrt_flatten_grid(const rrt_scene_desc* desc, int kind, int32_t res3[3], int32_t* n_items, int32_t* n_refs,
+                                int32_t* max_per_cell) {
+  if (kind < 0 || kind >= RRT_MAX_GRIDS) return fail(RRT_ERR_INVALID, "rrt_flatten_grid: kind must be 0 (spheres) or 1 (boxes)");
   FlatScene F;
   std::string err;
   int st = flatten_scene(desc, F, err);
   if (st != RRT_OK) return fail(st, "scene flatten failed: " + err);
-  int most = 0;
-  for (unsigned h : F.grid_cells) most = std::max(most, (int)(h & 255u));
-  const bool on = !F.grid_cells.empty();
-  if (res3) for (int a = 0; a < 3; ++a) res3[a] = on ? F.gres[a] : 0;
-  if (n_refs) *n_refs = on ? (int)F.grid_refs.size() : 0;
+  const bool on = (size_t)kind < F.grids.size() && F.grids[kind].n_items > 0;
+  int most = 0, refs = 0;
+  if (on) {
+    const DevGrid& G = F.grids[kind];
+    const size_t n_cells = (size_t)G.res[0] * G.res[1] * G.res[2];
+    for (size_t c = 0; c < n_cells; ++c) { const int k = (int)(F.grid_cells[G.first_cell + c] & 255u); most = std::max(most, k); refs += k; }
+  }
+  if (res3) for (int a = 0; a < 3; ++a) res3[a] = on ? F.grids[kind].res[a] : 0;
+  if (n_items) *n_items = on ? F.grids[kind].n_items : 0;
+  if (n_refs) *n_refs = refs;
   if (max_per_cell) *max_per_cell = most;
   return RRT_OK;
 }
@@ -702,40 +710,66 @@ extern "C" int rrt_flatten_check(const rrt_scene_desc* desc, int32_t* n_prims, i
   }
   for (int i = 0; i < F.n_prims; ++i)
     if (seen[i] != 1) return fail(RRT_ERR_INVALID, "flatten check: primitive not in exactly one leaf");
-  // the grid of a sphere field: every reference in range, every sphere of the tree referenced from every cell
-  // its box overlaps (so that a walk through the cells cannot miss it), nothing else referenced
-  if (!F.grid_cells.empty()) {
-    const size_t n_cells = (size_t)F.gres[0] * F.gres[1] * F.gres[2];
-    if (F.gres[0] < 1 || F.gres[1] < 1 || F.gres[2] < 1 || n_cells != F.grid_cells.size())
-      return fail(RRT_ERR_INVALID, "flatten check: grid resolution does not match its cell table");
-    std::vector<char> in_front(F.n_prims, 0);
-    { const int lf = ~F.front_ref, first = lf >> 8, n = ((lf >> 4) & 15) + (lf & 15); for (int k = 0; k < n; ++k) in_front[first + k] = 1; }
-    for (size_t c = 0; c < n_cells; ++c) {
-      const unsigned first = F.grid_cells[c] >> 8, cnt = F.grid_cells[c] & 255u;
-      if ((size_t)first + cnt > F.grid_refs.size()) return fail(RRT_ERR_INVALID, "flatten check: grid cell run out of range");
-      for (unsigned k = 0; k < cnt; ++k) {
-        const int p = F.grid_refs[first + k];
-        if (p < 0 || p >= F.n_prims || in_front[p]) return fail(RRT_ERR_INVALID, "flatten check: grid reference out of range");
+  // grids: every reference in range, every item referenced from every cell its bounds overlap (so that a walk
+  // through the cells cannot miss it), and — the render kernel walks no tree then — every primitive outside
+  // the front run in exactly one grid
+  if (!F.grids.empty()) {
+    std::vector<int> in_grid(F.n_prims, 0);
+    { const int lf = ~F.front_ref, first = lf >> 8, n = ((lf >> 4) & 15) + (lf & 15); for (int k = 0; k < n; ++k) in_grid[first + k] = -1000; }
+    const int n_box_recs = (int)(F.boxes.size() / 2);
+    for (size_t g = 0; g < F.grids.size(); ++g) {
+      const DevGrid& G = F.grids[g];
+      if (G.n_items <= 0) continue;
+      const size_t n_cells = (size_t)G.res[0] * G.res[1] * G.res[2];
+      if (G.res[0] < 1 || G.res[1] < 1 || G.res[2] < 1 || G.first_cell < 0 || (size_t)G.first_cell + n_cells > F.grid_cells.size())
+        return fail(RRT_ERR_INVALID, "flatten check: grid resolution does not match its cell table");
+      const int n_recs = G.kind == 1 ? n_box_recs : F.n_prims;
+      std::vector<char> member(n_recs, 0);
+      for (size_t c = 0; c < n_cells; ++c) {
+        const unsigned first = F.grid_cells[G.first_cell + c] >> 8, cnt = F.grid_cells[G.first_cell + c] & 255u;
+        if ((size_t)first + cnt > F.grid_refs.size()) return fail(RRT_ERR_INVALID, "flatten check: grid cell run out of range");
+        for (unsigned k = 0; k < cnt; ++k) {
+          const int p = F.grid_refs[first + k];
+          if (p < 0 || p >= n_recs) return fail(RRT_ERR_INVALID, "flatten check: grid reference out of range");
+          member[p] = 1;
+        }
       }
+      int n_members = 0;
+      for (int p = 0; p < n_recs; ++p) {
+        if (!member[p]) continue;
+        ++n_members;
+        float lo[3], hi[3];
+        if (G.kind == 1) {   // a box record and its six quads
+          const float4 b0 = F.boxes[2 * p], b1 = F.boxes[2 * p + 1];
+          lo[0] = b0.x; lo[1] = b0.y; lo[2] = b0.z; hi[0] = b1.x; hi[1] = b1.y; hi[2] = b1.z;
+          // the record is padded outwards and boxes that tile an axis own exactly their cell: test the box shrunk a little
+          for (int a = 0; a < 3; ++a) { const float e = 1e-3f * (hi[a] - lo[a]); lo[a] += e; hi[a] -= e; }
+          const int first = as_int(b0.w);
+          if (first < 0 || first + 6 > F.n_prims) return fail(RRT_ERR_INVALID, "flatten check: box record out of range");
+          for (int k = 0; k < 6; ++k) in_grid[first + k]++;
+        } else {             // a sphere's swept box, the f32 way the kernel sees it
+          const float4 p0 = F.prims[4 * p], p1 = F.prims[4 * p + 1];
+          const float c[3] = {p0.x, p0.y, p0.z}, d[3] = {p1.x, p1.y, p1.z};
+          for (int a = 0; a < 3; ++a) { lo[a] = std::min(c[a], c[a] + d[a]) - std::fabs(p0.w); hi[a] = std::max(c[a], c[a] + d[a]) + std::fabs(p0.w); }
+          in_grid[p]++;
+        }
+        int c0[3], c1[3];
+        for (int a = 0; a < 3; ++a) {
+          if (G.kind == 0 && (lo[a] < G.lo[a] || hi[a] > G.hi[a])) return fail(RRT_ERR_INVALID, "flatten check: sphere outside its grid");
+          c0[a] = std::max(0, std::min(G.res[a] - 1, (int)((lo[a] - G.lo[a]) * G.inv[a])));
+          c1[a] = std::max(0, std::min(G.res[a] - 1, (int)((hi[a] - G.lo[a]) * G.inv[a])));
+        }
+        for (int z = c0[2]; z <= c1[2]; ++z) for (int y = c0[1]; y <= c1[1]; ++y) for (int x = c0[0]; x <= c1[0]; ++x) {
+          const unsigned h = F.grid_cells[G.first_cell + ((size_t)z * G.res[1] + y) * G.res[0] + x];
+          bool found = false;
+          for (unsigned k = 0; k < (h & 255u); ++k) found |= F.grid_refs[(h >> 8) + k] == p;
+          if (!found) return fail(RRT_ERR_INVALID, "flatten check: item missing from a grid cell it overlaps");
+        }
+      }
+      if (n_members != G.n_items) return fail(RRT_ERR_INVALID, "flatten check: grid member count");
     }
-    for (int p = 0; p < F.n_prims; ++p) {
-      if (in_front[p]) continue;
-      const float4 p0 = F.prims[4 * p], p1 = F.prims[4 * p + 1];
-      const float c[3] = {p0.x, p0.y, p0.z}, d[3] = {p1.x, p1.y, p1.z};
-      int c0[3], c1[3];
-      for (int a = 0; a < 3; ++a) {   // the sphere's swept box in cell coordinates, the f32 way the kernel computes them
-        const float lo = std::min(c[a], c[a] + d[a]) - std::fabs(p0.w), hi = std::max(c[a], c[a] + d[a]) + std::fabs(p0.w);
-        if (lo < F.glo[a] || hi > F.ghi[a]) return fail(RRT_ERR_INVALID, "flatten check: sphere outside the grid");
-        c0[a] = std::max(0, std::min(F.gres[a] - 1, (int)((lo - F.glo[a]) * F.ginv[a])));
-        c1[a] = std::max(0, std::min(F.gres[a] - 1, (int)((hi - F.glo[a]) * F.ginv[a])));
-      }
-      for (int z = c0[2]; z <= c1[2]; ++z) for (int y = c0[1]; y <= c1[1]; ++y) for (int x = c0[0]; x <= c1[0]; ++x) {
-        const unsigned h = F.grid_cells[((size_t)z * F.gres[1] + y) * F.gres[0] + x];
-        bool found = false;
-        for (unsigned k = 0; k < (h & 255u); ++k) found |= F.grid_refs[(h >> 8) + k] == p;
-        if (!found) return fail(RRT_ERR_INVALID, "flatten check: sphere missing from a grid cell it overlaps");
-      }
-    }
+    for (int p = 0; p < F.n_prims; ++p)
+      if (in_grid[p] != 1 && in_grid[p] != -1000) return fail(RRT_ERR_INVALID, "flatten check: primitive neither in the front run nor in exactly one grid");
   }
   if (n_prims) *n_prims = F.n_prims;
   if (n_nodes) *n_nodes = nn;

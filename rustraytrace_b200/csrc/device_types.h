@@ -149,6 +149,16 @@ struct DevCamera64 {
   double c[3], p00[3], du[3], dv[3];
 };
 
+#define RRT_MAX_GRIDS 2
+struct DevGrid {
+  float lo[3], hi[3];     // bounds
+  float cell[3], inv[3];  // cell size and its reciprocal per axis
+  int res[3];
+  int first_cell;         // offset of this grid's cells in DevScene::grid_cells
+  int kind;               // 0: cells list spheres (flat primitive indices), 1: boxes (records of DevScene::boxes)
+  int n_items;
+};
+
 struct DevScene {
   const float4* prims;
   const float4* nodes;
@@ -170,17 +180,18 @@ struct DevScene {
   int n_nodes, n_prims, n_media, n_lights;
   int has_motion;    // any sphere with dc != 0
   int features;      // SceneFeature bits
-  // Uniform grid over the tree's primitives (flatten.cpp build_grid), or grid_cells == null.  A sphere field
-  // (the book-1 final scene, the bouncing spheres of book 2) is many primitives of one size spread evenly:
-  // a ray leaving the ground has to descend ~9 levels of any BVH to learn that its neighbourhood is empty,
-  // where a grid reads the cell it stands in.  cells[(z ry + y) rx + x] = first reference << 8 | count;
-  // refs[] = flat sphere indices.  Built for sphere-only trees the flattener finds evenly filled; the BVH
-  // stays (the f64 probe walks it, RRT_NO_GRID=1 renders with it).
+  // Uniform grids over even fields of equal primitives (flatten.cpp build_grids), n_grids == 0: none.
+  // A field — the 480 small spheres of the book-1 final scene, the 400 ground boxes and the 1 000-sphere
+  // cluster of the book-2 final scene — is many primitives of one size spread evenly: a ray has to descend
+  // ~10 levels of any BVH to learn that its neighbourhood is empty, where a grid reads the cell it stands in.
+  // With grids the render kernel walks no tree at all: whatever is not in a grid is in the front run
+  // (front_ref), tested by all lanes together.  The BVH over the grids' primitives stays for the f64 probe
+  // and for RRT_NO_GRID=1.  grid_cells[DevGrid::first_cell + (z ry + y) rx + x] = first reference << 8 |
+  // count; grid_refs[] = flat sphere indices (kind 0) or box records (kind 1).
   const unsigned* grid_cells;
   const int* grid_refs;
-  float glo[3], ghi[3];     // bounds of the grid
-  float gcell[3], ginv[3];  // cell size and its reciprocal per axis
-  int gres[3];
+  DevGrid grids[RRT_MAX_GRIDS];
+  int n_grids;
 };
 
 // One launch's share of the frame.

@@ -8,6 +8,7 @@
 #include <cmath>
 #include <cstring>
 #include <limits>
+#include <map>
 #include <queue>
 
 namespace rrt {
@@ -43,6 +44,7 @@ struct BakedPrim {
   double uvcos = 1, uvsin = 0;
   double lo[3], hi[3];
   int box = -1, face = -1;   // member of box group `box`, face slot 0..5 = -x,+x,-y,+y,-z,+z
+  int grid = -1;             // build item: member of uniform grid `grid` (0 spheres, 1 boxes), see build_grids
 };
 
 // Six quads that are exactly the faces of one axis-aligned box (quad.rs box_() under translations only).
@@ -588,78 +590,167 @@ bool tex_needs_ok(const rrt_scene_desc* d, int t, int depth) {
   return x.kind == RRT_T_SOLID;
 }
 
-// Uniform grid over the tree's items (device_types.h DevScene::grid_cells).  Only for trees of spheres that
-// fill it evenly: resolution from the item density (RRT_GRID_LAMBDA cells per item), every sphere referenced
-// from each cell its (padded) swept box overlaps.  Accepted when the result is balanced — few references per
-// sphere, no crowded cell — because that is when "read the cell you stand in" beats "descend the hierarchy":
-// measured on the book-1 final scene, C2 +15-18 % (profiles/README.md r02k).  RRT_NO_GRID=1 keeps the BVH,
-// RRT_FORCE_GRID=1 skips the balance test, RRT_GRID_LAMBDA=x overrides the density.
+// Uniform grids over even fields of equal items (device_types.h DevScene::grids).  Items of one kind and one
+// size class (spheres by radius, boxes by their longest edge, classes a factor of two wide) that number at
+// least RRT_GRID_MIN_ITEMS are a candidate field; its grid takes its resolution from the item density
+// (RRT_GRID_LAMBDA cells per item) and references every item from each cell its (padded) bounds overlap.
+// Accepted when balanced — few references per item, no crowded cell — because that is when "read the cell
+// you stand in" beats "descend the hierarchy" (profiles/README.md r02k).  At most one grid of spheres and one
+// of boxes.  RRT_NO_GRID=1 keeps the BVH, RRT_FORCE_GRID=1 skips the balance test, RRT_GRID_LAMBDA=x
+// overrides the density.
 #ifndef RRT_GRID_LAMBDA
 #define RRT_GRID_LAMBDA 0.5
+#endif
+#ifndef RRT_GRID_LAMBDA_BOX
+#define RRT_GRID_LAMBDA_BOX 0.5
 #endif
 #ifndef RRT_GRID_MIN_ITEMS
 #define RRT_GRID_MIN_ITEMS 64
 #endif
-void build_grid(const std::vector<BakedPrim>& items, const std::vector<int>& item_flat, FlatScene& out) {
-  out.grid_cells.clear(); out.grid_refs.clear();
-  for (int a = 0; a < 3; ++a) out.gres[a] = 0;
-  if (std::getenv("RRT_NO_GRID")) return;
-  const bool force = std::getenv("RRT_FORCE_GRID") != nullptr;
-  if (items.empty() || (items.size() < (size_t)RRT_GRID_MIN_ITEMS && !force)) return;
-  double lo[3], hi[3], mean_ext[3] = {0, 0, 0};
-  for (int a = 0; a < 3; ++a) { lo[a] = std::numeric_limits<double>::infinity(); hi[a] = -lo[a]; }
-  for (size_t i = 0; i < items.size(); ++i) {
-    if (items[i].kind != PRIM_SPHERE || item_flat[i] < 0) return;   // spheres only
+struct GridGeom {
+  double lo[3], hi[3], cell[3];
+  int res[3];
+  std::vector<std::vector<int>> lists;   // per cell: item indices
+  size_t n_refs = 0, crowded = 0;
+};
+// members: indices into items.  Returns false when the field is not worth a grid.
+bool grid_geometry(const std::vector<BakedPrim>& items, const std::vector<int>& members, bool force, GridGeom& G) {
+  if (members.empty()) return false;
+  double mean_ext[3] = {0, 0, 0};
+  for (int a = 0; a < 3; ++a) { G.lo[a] = std::numeric_limits<double>::infinity(); G.hi[a] = -G.lo[a]; }
+  for (int i : members)
     for (int a = 0; a < 3; ++a) {
-      lo[a] = std::min(lo[a], items[i].lo[a]); hi[a] = std::max(hi[a], items[i].hi[a]);
-      mean_ext[a] += (items[i].hi[a] - items[i].lo[a]) / (double)items.size();
+      G.lo[a] = std::min(G.lo[a], items[i].lo[a]); G.hi[a] = std::max(G.hi[a], items[i].hi[a]);
+      mean_ext[a] += (items[i].hi[a] - items[i].lo[a]) / (double)members.size();
     }
-  }
-  const char* le = std::getenv("RRT_GRID_LAMBDA");
-  const double lambda = le ? std::atof(le) : RRT_GRID_LAMBDA;
+  const bool of_boxes = items[members[0]].kind == ITEM_BOX;
+  const char* le = std::getenv(of_boxes ? "RRT_GRID_LAMBDA_BOX" : "RRT_GRID_LAMBDA");
+  const double lambda = le ? std::atof(le) : (of_boxes ? RRT_GRID_LAMBDA_BOX : RRT_GRID_LAMBDA);
   // a flat field is one cell thick: an axis no longer than the items themselves gets the items' extent
   double ext[3], vol = 1;
-  for (int a = 0; a < 3; ++a) { ext[a] = std::max(hi[a] - lo[a], std::max(mean_ext[a], 1e-9)); vol *= ext[a]; }
-  const double dens = std::cbrt(lambda * (double)items.size() / vol);
-  int res[3];
-  double cell[3];
-  for (int a = 0; a < 3; ++a) {
-    res[a] = std::max(1, std::min(128, (int)std::lround(ext[a] * dens)));
-    const double pad = 1e-3 * ext[a] / res[a] + 1e-6 * std::max(std::fabs(lo[a]), std::fabs(hi[a]));   // the bounds, outwards
-    lo[a] -= pad; hi[a] += pad;
-    cell[a] = (hi[a] - lo[a]) / res[a];
+  for (int a = 0; a < 3; ++a) { ext[a] = std::max(G.hi[a] - G.lo[a], std::max(mean_ext[a], 1e-9)); vol *= ext[a]; }
+  const double dens = std::cbrt(lambda * (double)members.size() / vol);
+  // Boxes that tile an axis exactly (the 20 x 20 ground boxes of the book-2 final scene, the_next_week/mod.rs:309-327:
+  // equal widths at whole multiples of the width) get cells that ARE the tiles along that axis: one box per cell
+  // instead of the nine a padded membership would list.  The walk can then differ from the tree only for a ray that
+  // passes within f32 rounding of a vertical box edge, where either answer is a rounding of the same silhouette.
+  bool tiled[3] = {false, false, false};
+  double tile_lo[3] = {0, 0, 0}, tile_w[3] = {0, 0, 0};
+  if (of_boxes && !std::getenv("RRT_GRID_NO_TILING")) {
+    for (int a = 0; a < 3; ++a) {
+      const BakedPrim& f = items[members[0]];
+      const double wd = f.dc[a] - f.c0[a];
+      double flo = std::numeric_limits<double>::infinity(), fhi = -flo;
+      bool same = wd > 0;
+      for (int i : members) {
+        same = same && std::fabs((items[i].dc[a] - items[i].c0[a]) - wd) <= 1e-9 * wd;
+        flo = std::min(flo, items[i].c0[a]); fhi = std::max(fhi, items[i].dc[a]);
+      }
+      if (!same) continue;
+      const double n = (fhi - flo) / wd;
+      if (n < 2 || n > 128 || std::fabs(n - std::round(n)) > 1e-6) continue;
+      bool on_lattice = true;
+      for (int i : members) { const double k = (items[i].c0[a] - flo) / wd; on_lattice = on_lattice && std::fabs(k - std::round(k)) <= 1e-6; }
+      if (!on_lattice) continue;
+      tiled[a] = true; tile_lo[a] = flo; tile_w[a] = wd;
+      G.res[a] = (int)std::lround(n); G.lo[a] = flo; G.hi[a] = fhi; G.cell[a] = wd;
+    }
   }
-  const size_t n_cells = (size_t)res[0] * res[1] * res[2];
-  std::vector<std::vector<int>> lists(n_cells);
-  size_t n_refs = 0;
-  for (size_t i = 0; i < items.size(); ++i) {
+  for (int a = 0; a < 3; ++a) {
+    if (tiled[a]) continue;
+    G.res[a] = std::max(1, std::min(128, (int)std::lround(ext[a] * dens)));
+    const double pad = 1e-3 * ext[a] / G.res[a] + 1e-6 * std::max(std::fabs(G.lo[a]), std::fabs(G.hi[a]));   // the bounds, outwards
+    G.lo[a] -= pad; G.hi[a] += pad;
+    G.cell[a] = (G.hi[a] - G.lo[a]) / G.res[a];
+  }
+  G.lists.assign((size_t)G.res[0] * G.res[1] * G.res[2], std::vector<int>());
+  G.n_refs = 0; G.crowded = 0;
+  for (int i : members) {
     int c0[3], c1[3];
     for (int a = 0; a < 3; ++a) {
+      if (tiled[a]) { c0[a] = c1[a] = std::max(0, std::min(G.res[a] - 1, (int)std::lround((items[i].c0[a] - tile_lo[a]) / tile_w[a]))); continue; }
       // padded by a thousandth of a cell: the f32 walk may leave a cell that far from where f64 would
-      const double pad = 1e-3 * cell[a] + 4e-7 * std::max(std::fabs(items[i].lo[a]), std::fabs(items[i].hi[a]));
-      c0[a] = std::max(0, std::min(res[a] - 1, (int)std::floor((items[i].lo[a] - pad - lo[a]) / cell[a])));
-      c1[a] = std::max(0, std::min(res[a] - 1, (int)std::floor((items[i].hi[a] + pad - lo[a]) / cell[a])));
+      const double pad = 1e-3 * G.cell[a] + 4e-6 * std::max(std::fabs(items[i].lo[a]), std::fabs(items[i].hi[a]));
+      c0[a] = std::max(0, std::min(G.res[a] - 1, (int)std::floor((items[i].lo[a] - pad - G.lo[a]) / G.cell[a])));
+      c1[a] = std::max(0, std::min(G.res[a] - 1, (int)std::floor((items[i].hi[a] + pad - G.lo[a]) / G.cell[a])));
     }
     for (int z = c0[2]; z <= c1[2]; ++z)
       for (int y = c0[1]; y <= c1[1]; ++y)
-        for (int x = c0[0]; x <= c1[0]; ++x) { lists[((size_t)z * res[1] + y) * res[0] + x].push_back(item_flat[i]); ++n_refs; }
+        for (int x = c0[0]; x <= c1[0]; ++x) { G.lists[((size_t)z * G.res[1] + y) * G.res[0] + x].push_back(i); ++G.n_refs; }
   }
-  size_t crowded = 0;
-  for (const std::vector<int>& l : lists) crowded = std::max(crowded, l.size());
-  if (crowded > 255 || n_refs >= (1u << 24)) return;
-  if (!force && ((double)n_refs > 4.0 * (double)items.size() || crowded > 12)) return;   // not an even field
-  out.grid_cells.resize(n_cells);
-  out.grid_refs.reserve(n_refs + 1);
-  for (size_t c = 0; c < n_cells; ++c) {
-    out.grid_cells[c] = ((unsigned)out.grid_refs.size() << 8) | (unsigned)lists[c].size();
-    for (int r : lists[c]) out.grid_refs.push_back(r);
+  for (const std::vector<int>& l : G.lists) G.crowded = std::max(G.crowded, l.size());
+  if (std::getenv("RRT_GRID_DEBUG"))
+    std::fprintf(stderr, "grid candidate: %zu items, %dx%dx%d cells, %.2f references per item, most in a cell %zu\n", members.size(),
+                 G.res[0], G.res[1], G.res[2], (double)G.n_refs / (double)members.size(), G.crowded);
+  if (G.crowded > 255 || G.n_refs >= (1u << 22)) return false;
+  if (!force && ((double)G.n_refs > 8.0 * (double)members.size() || G.crowded > 64)) return false;   // not an even field
+  return true;
+}
+
+// Tags the members of the chosen fields (BakedPrim::grid = 0 for the sphere grid, 1 for the box grid).  Grids are
+// only adopted when everything else fits the front run (the kernel then walks no tree): returns the number adopted.
+int choose_grids(std::vector<BakedPrim>& items) {
+  if (std::getenv("RRT_NO_GRID") || std::getenv("RRT_NO_FRONT")) return 0;   // (what is not in a grid goes to the front run)
+  const bool force = std::getenv("RRT_FORCE_GRID") != nullptr;
+  int adopted = 0;
+  for (int kind = 0; kind < 2; ++kind) {   // 0: spheres, 1: boxes
+    std::map<int, std::vector<int>> classes;
+    for (size_t i = 0; i < items.size(); ++i) {
+      const BakedPrim& p = items[i];
+      if (kind == 0 ? p.kind != PRIM_SPHERE : p.kind != ITEM_BOX) continue;
+      double size = kind == 0 ? p.r : std::max(p.hi[0] - p.lo[0], std::max(p.hi[1] - p.lo[1], p.hi[2] - p.lo[2]));
+      if (!(size > 0)) continue;
+      classes[force ? 0 : (int)std::floor(std::log2(size))].push_back((int)i);
+    }
+    const std::vector<int>* best = nullptr;
+    for (const auto& kv : classes) if (!best || kv.second.size() > best->size()) best = &kv.second;
+    if (!best || (best->size() < (size_t)RRT_GRID_MIN_ITEMS && !force)) continue;
+    GridGeom G;
+    if (!grid_geometry(items, *best, force, G)) continue;
+    for (int i : *best) items[i].grid = kind;
+    ++adopted;
   }
+  if (!adopted) return 0;
+  int ns = 0, nq = 0, nb = 0;
+  for (const BakedPrim& p : items) if (p.grid < 0) (p.kind == PRIM_SPHERE ? ns : p.kind == ITEM_BOX ? nb : nq)++;
+  if (ns > LEAF_MAX_PER_KIND || nq > LEAF_MAX_PER_KIND || nb > 0) {   // the rest does not fit the front run
+    for (BakedPrim& p : items) p.grid = -1;
+    return 0;
+  }
+  return adopted;
+}
+
+// After the primitives are emitted: the chosen grids with their cell tables (item_ref: build item -> flat sphere
+// index or box record).
+void emit_grids(const std::vector<BakedPrim>& items, const std::vector<int>& item_ref, FlatScene& out) {
+  out.grid_cells.clear(); out.grid_refs.clear(); out.grids.clear();
+  const bool force = std::getenv("RRT_FORCE_GRID") != nullptr;
+  std::vector<DevGrid> slots(RRT_MAX_GRIDS);
+  int present = 0;
+  for (int kind = 0; kind < RRT_MAX_GRIDS; ++kind) {
+    DevGrid& D = slots[kind];
+    std::memset(&D, 0, sizeof D);
+    D.kind = kind;
+    std::vector<int> members;
+    for (size_t i = 0; i < items.size(); ++i) if (items[i].grid == kind) members.push_back((int)i);
+    GridGeom G;
+    if (members.empty() || !grid_geometry(items, members, force, G)) continue;
+    D.first_cell = (int)out.grid_cells.size();
+    D.n_items = (int)members.size();
+    for (const std::vector<int>& l : G.lists) {
+      out.grid_cells.push_back(((unsigned)out.grid_refs.size() << 8) | (unsigned)l.size());
+      for (int i : l) out.grid_refs.push_back(item_ref[i]);
+    }
+    for (int a = 0; a < 3; ++a) {
+      D.lo[a] = (float)G.lo[a]; D.hi[a] = (float)G.hi[a];
+      D.cell[a] = (float)G.cell[a]; D.inv[a] = (float)(1.0 / G.cell[a]);
+      D.res[a] = G.res[a];
+    }
+    ++present;
+  }
+  if (!present) { out.grid_cells.clear(); out.grid_refs.clear(); return; }
   if (out.grid_refs.empty()) out.grid_refs.push_back(0);
-  for (int a = 0; a < 3; ++a) {
-    out.glo[a] = (float)lo[a]; out.ghi[a] = (float)hi[a];
-    out.gcell[a] = (float)((hi[a] - lo[a]) / res[a]); out.ginv[a] = (float)(res[a] / (hi[a] - lo[a]));
-    out.gres[a] = res[a];
-  }
+  out.grids = slots;   // both slots, an absent one has n_items == 0
 }
 
 }  // namespace
@@ -811,6 +902,7 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
       BakedPrim it;
       it.kind = ITEM_BOX; it.box = (int)g;
       for (int a = 0; a < 3; ++a) { it.lo[a] = w.boxes[g].lo[a]; it.hi[a] = w.boxes[g].hi[a]; }
+      it.c0 = D3(w.boxes[g].lo[0], w.boxes[g].lo[1], w.boxes[g].lo[2]); it.dc = D3(w.boxes[g].hi[0], w.boxes[g].hi[1], w.boxes[g].hi[2]);   // the box itself (grid tiling test)
       for (int s = 0; s < 6; ++s)   // the faces' own (padded) bounds, as the reference's list box has them
         for (int a = 0; a < 3; ++a) { it.lo[a] = std::min(it.lo[a], P[w.boxes[g].member[s]].lo[a]); it.hi[a] = std::max(it.hi[a], P[w.boxes[g].member[s]].hi[a]); }
       items.push_back(it); item_src.push_back(-1 - (int)g);
@@ -827,7 +919,14 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
   // the book-2 final scene measured 1.6 % slower.  Repeated on what is left, because without the
   // ground sphere the bounds are those of the rest.  At most FRONT_MAX primitives.
   int n_front = 0;
-  if (!single && !std::getenv("RRT_NO_FRONT")) {
+  const int n_grids_chosen = single ? 0 : choose_grids(items);
+  if (n_grids_chosen > 0) {   // everything outside the grids is the front run: the render kernel walks no tree
+    std::vector<BakedPrim> it2; std::vector<int> src2;
+    for (int pass = 0; pass < 2; ++pass)
+      for (size_t i = 0; i < items.size(); ++i)
+        if ((items[i].grid < 0) == (pass == 0)) { it2.push_back(items[i]); src2.push_back(item_src[i]); if (pass == 0) ++n_front; }
+    items.swap(it2); item_src.swap(src2);
+  } else if (!single && !std::getenv("RRT_NO_FRONT")) {
     bool spheres_only = true;
     for (const BakedPrim& p : items) if (p.kind != PRIM_SPHERE) spheres_only = false;
     const double share = spheres_only ? RRT_FRONT_SHARE_SPHERES : RRT_FRONT_SHARE_OTHER;
@@ -874,7 +973,7 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
   out.bvh_depth = B.max_depth_seen;
   // leaf -> contiguous prim run (spheres first, then quads); prims emitted in `order` sequence
   std::vector<int> leaf_ref(B.nodes.size(), 0);
-  std::vector<int> item_flat(items.size(), -1);   // tree item -> flat primitive index (box groups: -1)
+  std::vector<int> item_flat(items.size(), -1);   // tree item -> flat primitive index (box groups: their box record)
   {
     // emit prims leaf by leaf in B.order sequence (DFS), reordering within the leaf by kind
     int emitted = 0;
@@ -900,6 +999,7 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
         float4 b0 = f4(lo[0], lo[1], lo[2], 0), b1 = f4(hi[0], hi[1], hi[2], 0);
         std::memcpy(&b0.w, &emitted, 4);
         leaf_ref[li] = ~(((int)(out.boxes.size() / 2) << 8) | LEAF_BOX_MARK);
+        item_flat[B.order[n.first]] = (int)(out.boxes.size() / 2);   // a box item is known by its record
         out.boxes.push_back(b0); out.boxes.push_back(b1);
         for (int s = 0; s < 6; ++s) { emit_prim32(P[g.member[s]], out.prims); emit_prim64(P[g.member[s]], out.prims64); }
         emitted += 6;
@@ -966,7 +1066,7 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
     out.nodes.push_back(i4(ref0, ref1, 0, 0));
   }
   out.root_ref = 0;
-  build_grid(items, item_flat, out);
+  if (n_grids_chosen > 0) emit_grids(items, item_flat, out);
 #ifdef RRT_BVH4
   // Experiment (profiles/README.md, r02): the binary tree collapsed to 4-wide nodes — a node's children
   // are its grandchildren (a leaf child stays one child) — so that a traversal step tests four boxes with

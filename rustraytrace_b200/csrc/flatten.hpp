@@ -18,10 +18,9 @@ struct FlatScene {
   std::vector<float4> nodes;      // 4 per inner node
   std::vector<float4> nodes4;     // -DRRT_BVH4 experiment only: 8 per 4-wide node
   std::vector<float4> qpairs;     // root-leaf quads again, 6 float4 per pair (device_types.h)
-  std::vector<unsigned> grid_cells;  // uniform grid over the tree's spheres (device_types.h DevScene), or empty
+  std::vector<unsigned> grid_cells;  // uniform grids over even fields of spheres / boxes (device_types.h DevScene), pooled; or empty
   std::vector<int> grid_refs;
-  float glo[3] = {0, 0, 0}, ghi[3] = {0, 0, 0}, gcell[3] = {0, 0, 0}, ginv[3] = {0, 0, 0};
-  int gres[3] = {0, 0, 0};
+  std::vector<DevGrid> grids;        // at most RRT_MAX_GRIDS
   std::vector<float4> bprims;     // 4 per medium-boundary prim
   std::vector<DevMaterial> materials;
   std::vector<DevTexture> textures;

@@ -258,39 +258,42 @@ __device__ __forceinline__ void leaf1_hit32(const float4* __restrict__ prims, co
   else quad_hit32(prims, leaf >> 8, r, tmin, skip, h);
 }
 
-// The uniform grid of a sphere field (device_types.h DevScene::grid_cells, flatten.cpp build_grid): clip the ray
-// to the grid, then walk the cells it crosses front to back (Amanatides & Woo) and test the spheres each
-// cell references, until the next cell begins behind the closest hit.  A sphere referenced by several
-// cells is tested in each — sphere_hit32's result does not depend on order or repetition, so the hit and
-// the equal-t rule are those of the tree walk.
-__device__ __forceinline__ void grid_hit32(const DevScene& S, const Ray32& r, float a, float inv_a, float tmin, int skip,
-                                           bool motion, Hit32& h) {
-  const float idx = safe_rcp(r.d.x), idy = safe_rcp(r.d.y), idz = safe_rcp(r.d.z);
-  const float x0 = (S.glo[0] - r.o.x) * idx, x1 = (S.ghi[0] - r.o.x) * idx;
-  const float y0 = (S.glo[1] - r.o.y) * idy, y1 = (S.ghi[1] - r.o.y) * idy;
-  const float z0 = (S.glo[2] - r.o.z) * idz, z1 = (S.ghi[2] - r.o.z) * idz;
+// One uniform grid of an even field (device_types.h DevGrid, flatten.cpp choose_grids / emit_grids): clip the ray
+// to the grid, then walk the cells it crosses front to back (Amanatides & Woo) and test what each cell
+// references — spheres (KIND 0) or boxes (KIND 1, the box-leaf test) — until the next cell begins behind the
+// closest hit.  An item referenced by several cells is tested in each: sphere_hit32 / quad_hit32 do not
+// depend on order or repetition, so the hit and the equal-t rule are those of the tree walk.
+template <int FEAT, int KIND>
+__device__ __forceinline__ void grid_hit32(const DevScene& S, const DevGrid& G, const Ray32& r, float idx, float idy, float idz,
+                                           float a, float inv_a, float tmin, int skip, bool motion, Hit32& h) {
+  const float x0 = (G.lo[0] - r.o.x) * idx, x1 = (G.hi[0] - r.o.x) * idx;
+  const float y0 = (G.lo[1] - r.o.y) * idy, y1 = (G.hi[1] - r.o.y) * idy;
+  const float z0 = (G.lo[2] - r.o.z) * idz, z1 = (G.hi[2] - r.o.z) * idz;
   const float t0 = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
   const float t1 = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), h.t));
   if (!(t0 <= t1)) return;
-  const int rx = S.gres[0], ry = S.gres[1], rz = S.gres[2];
-  int ix = min(max((int)((fmaf(t0, r.d.x, r.o.x) - S.glo[0]) * S.ginv[0]), 0), rx - 1);
-  int iy = min(max((int)((fmaf(t0, r.d.y, r.o.y) - S.glo[1]) * S.ginv[1]), 0), ry - 1);
-  int iz = min(max((int)((fmaf(t0, r.d.z, r.o.z) - S.glo[2]) * S.ginv[2]), 0), rz - 1);
+  const int rx = G.res[0], ry = G.res[1], rz = G.res[2];
+  int ix = min(max((int)((fmaf(t0, r.d.x, r.o.x) - G.lo[0]) * G.inv[0]), 0), rx - 1);
+  int iy = min(max((int)((fmaf(t0, r.d.y, r.o.y) - G.lo[1]) * G.inv[1]), 0), ry - 1);
+  int iz = min(max((int)((fmaf(t0, r.d.z, r.o.z) - G.lo[2]) * G.inv[2]), 0), rz - 1);
   const bool px = r.d.x >= 0.0f, py = r.d.y >= 0.0f, pz = r.d.z >= 0.0f;
   // parameter at which the ray leaves the current cell along each axis, and its increment per cell
-  float tmx = (fmaf((float)(ix + (px ? 1 : 0)), S.gcell[0], S.glo[0]) - r.o.x) * idx;
-  float tmy = (fmaf((float)(iy + (py ? 1 : 0)), S.gcell[1], S.glo[1]) - r.o.y) * idy;
-  float tmz = (fmaf((float)(iz + (pz ? 1 : 0)), S.gcell[2], S.glo[2]) - r.o.z) * idz;
-  const float tdx = S.gcell[0] * fabsf(idx), tdy = S.gcell[1] * fabsf(idy), tdz = S.gcell[2] * fabsf(idz);
+  float tmx = (fmaf((float)(ix + (px ? 1 : 0)), G.cell[0], G.lo[0]) - r.o.x) * idx;
+  float tmy = (fmaf((float)(iy + (py ? 1 : 0)), G.cell[1], G.lo[1]) - r.o.y) * idy;
+  float tmz = (fmaf((float)(iz + (pz ? 1 : 0)), G.cell[2], G.lo[2]) - r.o.z) * idz;
+  const float tdx = G.cell[0] * fabsf(idx), tdy = G.cell[1] * fabsf(idy), tdz = G.cell[2] * fabsf(idz);
   const int sx = px ? 1 : -1, sy = py ? rx : -rx, sz = pz ? rx * ry : -(rx * ry);
   // cells still to cross along each axis before the ray leaves the grid
   int nx = px ? rx - 1 - ix : ix, ny = py ? ry - 1 - iy : iy, nz = pz ? rz - 1 - iz : iz;
-  int cell = (iz * ry + iy) * rx + ix;
+  int cell = G.first_cell + (iz * ry + iy) * rx + ix;
   for (;;) {
     const unsigned hdr = __ldg(S.grid_cells + cell);
     const int* refs = S.grid_refs + (hdr >> 8);
     const int cnt = (int)(hdr & 255u);
-    for (int k = 0; k < cnt; ++k) sphere_hit32(S.prims, __ldg(refs + k), r, a, inv_a, tmin, skip, motion, h);
+    for (int k = 0; k < cnt; ++k) {
+      if (KIND == 0) sphere_hit32(S.prims, __ldg(refs + k), r, a, inv_a, tmin, skip, motion, h);
+      else box_leaf_hit32(S.prims, S.boxes, __ldg(refs + k), r, V3f(idx, idy, idz), tmin, skip, h);
+    }
     const bool bx = tmx <= tmy && tmx <= tmz, by = !bx && tmy <= tmz;
     const float tn = bx ? tmx : (by ? tmy : tmz);
     int left;
@@ -315,8 +318,12 @@ __device__ inline void world_hit32(const DevScene& S, const Ray32& r, float tmin
   }
   // front run (flatten.cpp): primitives spanning most of the scene, tested by all lanes together
   if (S.front_ref != -1) leaf_hit32<FEAT>(S.prims, S.boxes, ~S.front_ref, r, V3f(0.0f, 0.0f, 0.0f), a, inv_a, tmin, skip, motion, h);
-  if (S.grid_cells) { grid_hit32(S, r, a, inv_a, tmin, skip, motion, h); return; }   // an even sphere field: cells instead of the tree
   const float idx = safe_rcp(r.d.x), idy = safe_rcp(r.d.y), idz = safe_rcp(r.d.z);
+  if (S.n_grids > 0) {   // even fields in grids, the rest in the front run above: no tree to walk
+    if (S.grids[0].n_items > 0) grid_hit32<FEAT, 0>(S, S.grids[0], r, idx, idy, idz, a, inv_a, tmin, skip, motion, h);
+    if ((FEAT & SF_BOXES) && S.grids[1].n_items > 0) grid_hit32<FEAT, 1>(S, S.grids[1], r, idx, idy, idz, a, inv_a, tmin, skip, motion, h);
+    return;
+  }
   float oodx = r.o.x * idx, oody = r.o.y * idy, oodz = r.o.z * idz;
   asm("" : "+f"(oodx), "+f"(oody), "+f"(oodz));  // opaque: keep in registers, do not rematerialise in the loop
   int stack[RRT_STACK];

@@ -5,6 +5,8 @@ mkdir -p gpurun_out
 T=r02k
 python -m pytest tests -m gpu -q -x > gpurun_out/${T}_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/${T}_pytest.log
 tail -6 gpurun_out/${T}_pytest.log
+python -m pytest tests/test_zz_no_alloc.py -m gpu -q > gpurun_out/${T}_pytest_noalloc_alone.log 2>&1; echo "alone rc=$?" >> gpurun_out/${T}_pytest_noalloc_alone.log
+tail -4 gpurun_out/${T}_pytest_noalloc_alone.log
 python scripts/gpu_quick.py 64 > gpurun_out/${T}_quick64.log 2>&1
 RRT_NO_GRID=1 python scripts/gpu_quick.py 64 C1,C2,C3a > gpurun_out/${T}_quick64_nogrid.log 2>&1
 python scripts/gpu_quick.py 500 C2,C3a,C4,C5 > gpurun_out/${T}_quick500.log 2>&1

@@ -15,7 +15,8 @@
 //   RRT_NO_FRONT=1 build/warp_sim 1 -1 1200       # the same rays against the tree without a front run
 // Scheduling variants (environment): SIM_NO_CHAIN / SIM_CHAIN (consecutive leaves in one round off / on),
 // SIM_DEFER=k (a lane puts k leaves aside before it waits), SIM_MAX_LEAF, SIM_SINGLE_LEAF_MAX,
-// SIM_TILE=WxH (pixels of a warp's tile), SIM_REGEN_MIN=k (dead lanes start new paths k at a time).
+// SIM_TILE=WxH (pixels of a warp's tile), SIM_REGEN_MIN=k (dead lanes start new paths k at a time),
+// SIM_QUEUE=1 [SIM_SORT=w] [SIM_POOL=n] (decoupled ray queue), SIM_GRID=lambda (uniform grid instead of the tree).
 //
 // Not part of the product and not an oracle: sphere/quad hits and the three book-1 materials in f32,
 // no textures (albedo from the material record), no media, no light sampling.  Validation against the
@@ -486,6 +487,94 @@ int main(int argc, char** argv) {
     std::printf("QUEUE model (pool %d): traversal %.0f + front %.0f + shade/regen %.0f = %.0f warp instructions per 32 segments; node steps per 32 segments %.2f (lane occupancy %.0f %%)\n",
                 pool, 32 * qcost / nseg, 32 * front_cost / nseg, 32 * shade_cost / nseg, 32 * (qcost + front_cost + shade_cost) / nseg, 32 * qsteps / nseg, 100.0 * lane_active / (32.0 * qsteps));
     std::printf("QUEUE vs kernel, warp instructions per segment-lane: %.1f vs %.1f\n", (qcost + front_cost + shade_cost) / nseg, cost / lanes);
+  }
+  // ---- SIM_GRID=lambda: the tree replaced by a uniform grid over its spheres (what flatten.cpp build_grid builds) ----
+  if (const char* ge = std::getenv("SIM_GRID")) {
+    const double lambda = std::atof(ge);
+    struct Box { float lo[3], hi[3]; int prim; };
+    std::vector<Box> items;
+    std::vector<char> in_front(T.F.n_prims, 0);
+    if (T.F.front_ref != -1) { int lf = ~T.F.front_ref, first = lf >> 8, n = ((lf >> 4) & 15) + (lf & 15); for (int k = 0; k < n; ++k) in_front[first + k] = 1; }
+    for (int i = 0; i < T.F.n_prims; ++i) {
+      if (in_front[i]) continue;
+      const float4 p0 = T.F.prims[4 * i], p1 = T.F.prims[4 * i + 1];
+      Box b; b.prim = i;
+      const float c[3] = {p0.x, p0.y, p0.z}, d[3] = {p1.x, p1.y, p1.z};
+      for (int a = 0; a < 3; ++a) { b.lo[a] = std::min(c[a], c[a] + d[a]) - std::fabs(p0.w); b.hi[a] = std::max(c[a], c[a] + d[a]) + std::fabs(p0.w); }
+      items.push_back(b);
+    }
+    float glo[3] = {1e30f, 1e30f, 1e30f}, ghi[3] = {-1e30f, -1e30f, -1e30f};
+    double avg_ext[3] = {0, 0, 0};
+    for (const Box& b : items) for (int a = 0; a < 3; ++a) { glo[a] = std::min(glo[a], b.lo[a]); ghi[a] = std::max(ghi[a], b.hi[a]); avg_ext[a] += (b.hi[a] - b.lo[a]) / items.size(); }
+    double ext[3], V = 1;
+    for (int a = 0; a < 3; ++a) { ext[a] = std::max<double>(ghi[a] - glo[a], avg_ext[a]); V *= ext[a]; }
+    const double dens = std::cbrt(lambda * items.size() / V);
+    int res[3]; float cell[3], inv_cell[3];
+    for (int a = 0; a < 3; ++a) { res[a] = std::max(1, std::min(256, (int)std::lround(ext[a] * dens))); cell[a] = (ghi[a] - glo[a]) / res[a]; inv_cell[a] = res[a] / std::max(1e-20f, ghi[a] - glo[a]); }
+    std::vector<std::vector<int>> cells((size_t)res[0] * res[1] * res[2]);
+    size_t refs = 0;
+    for (const Box& b : items) {
+      int c0[3], c1[3];
+      for (int a = 0; a < 3; ++a) { c0[a] = std::max(0, std::min(res[a] - 1, (int)((b.lo[a] - glo[a]) * inv_cell[a]))); c1[a] = std::max(0, std::min(res[a] - 1, (int)((b.hi[a] - glo[a]) * inv_cell[a]))); }
+      for (int z = c0[2]; z <= c1[2]; ++z) for (int y = c0[1]; y <= c1[1]; ++y) for (int x = c0[0]; x <= c1[0]; ++x) { cells[((size_t)z * res[1] + y) * res[0] + x].push_back(b.prim); ++refs; }
+    }
+    std::printf("GRID %dx%dx%d over %zu items, %.2f references per item, %.2f per cell\n", res[0], res[1], res[2], items.size(), (double)refs / items.size(), (double)refs / cells.size());
+    const double G_SETUP = 45, G_CELL = 24, G_SPH = 30;   // instruction prices: clip + set-up, one cell step, one sphere test
+    double gcost = 0, gl = 0, tot_cells = 0, tot_tests = 0, warp_cells = 0, warp_tests = 0, wrong = 0;
+    for (const Iter& it : iters) {
+      std::vector<std::vector<int>> per_cell(it.lanes.size());
+      size_t R = 0;
+      int nfront = 0;
+      for (size_t k = 0; k < it.lanes.size(); ++k) {
+        const Seg& sg = it.lanes[k];
+        const Ray& r = sg.r;
+        const int skip = sg.skip_id >= 0 ? T.id_to_flat[sg.skip_id] : -1;
+        Hit h{INFINITY, -1};
+        const float a = dot(r.d, r.d), inv_a = 1.0f / a;
+        if (T.F.front_ref != -1) { leaf_hit(T.F, ~T.F.front_ref, r, a, inv_a, 0.001f, skip, h); nfront = ((~T.F.front_ref >> 4) & 15) + (~T.F.front_ref & 15); }
+        const float o[3] = {r.o.x, r.o.y, r.o.z}, d[3] = {r.d.x, r.d.y, r.d.z};
+        float t0 = 0.001f, t1 = h.t;
+        for (int ax = 0; ax < 3; ++ax) {
+          const float id = 1.0f / (std::fabs(d[ax]) > 1e-30f ? d[ax] : std::copysign(1e-30f, d[ax]));
+          float ta = (glo[ax] - o[ax]) * id, tb = (ghi[ax] - o[ax]) * id;
+          if (ta > tb) std::swap(ta, tb);
+          t0 = std::max(t0, ta); t1 = std::min(t1, tb);
+        }
+        std::vector<int>& pc = per_cell[k];
+        if (t0 <= t1) {
+          int ic[3], stp[3]; float tmax[3], tdel[3];
+          for (int ax = 0; ax < 3; ++ax) {
+            const float p = o[ax] + t0 * d[ax];
+            ic[ax] = std::max(0, std::min(res[ax] - 1, (int)((p - glo[ax]) * inv_cell[ax])));
+            const float id = 1.0f / (std::fabs(d[ax]) > 1e-30f ? d[ax] : std::copysign(1e-30f, d[ax]));
+            stp[ax] = d[ax] >= 0 ? 1 : -1;
+            tmax[ax] = (glo[ax] + (ic[ax] + (d[ax] >= 0 ? 1 : 0)) * cell[ax] - o[ax]) * id; tdel[ax] = cell[ax] * std::fabs(id);
+          }
+          for (;;) {
+            const std::vector<int>& c = cells[((size_t)ic[2] * res[1] + ic[1]) * res[0] + ic[0]];
+            pc.push_back((int)c.size());
+            for (int pi : c) sphere_hit(T.F, pi, r, a, inv_a, 0.001f, skip, h);
+            const int ax = tmax[0] < tmax[1] ? (tmax[0] < tmax[2] ? 0 : 2) : (tmax[1] < tmax[2] ? 1 : 2);
+            if (tmax[ax] > std::min(t1, h.t)) break;
+            ic[ax] += stp[ax]; tmax[ax] += tdel[ax];
+            if (ic[ax] < 0 || ic[ax] >= res[ax]) break;
+          }
+        }
+        if (world_hit(T, r, 0.001f, skip, nullptr).prim != h.prim) wrong += 1;   // same closest hit as the tree?
+        R = std::max(R, pc.size());
+        tot_cells += pc.size(); for (int v : pc) tot_tests += v;
+      }
+      double c = C_SETUP + C_FIXED + C_FRONT * nfront + G_SETUP;
+      for (size_t q = 0; q < R; ++q) {
+        int mt = 0;
+        for (const auto& pc : per_cell) if (q < pc.size()) mt = std::max(mt, pc[q]);
+        c += G_CELL + G_SPH * mt; warp_cells += 1; warp_tests += mt;
+      }
+      gcost += c; gl += it.lanes.size();
+    }
+    const double nI = (double)iters.size();
+    std::printf("GRID per warp and segment: %.2f cell rounds (%.2f per lane), %.2f sphere tests (%.2f per lane) | modelled %.0f warp instructions; %.0f of %.0f closest hits differ from the tree's\n",
+                warp_cells / nI, tot_cells / gl, warp_tests / nI, tot_tests / gl, gcost / nI, wrong, gl);
   }
   const double ni = (double)iters.size();
   std::printf("scene book %d/%d width %d: %d prims, %zu nodes, front run %d, chain %d | %.0f paths, %.2f segments per path, %.1f lanes per warp iteration\n",

@@ -123,7 +123,8 @@ def test_outsized_primitives_leave_the_tree(monkeypatch):
     """Front run (flatten.cpp): the r = 1000 ground sphere and the three r = 1 spheres of the book-1
     scene (in_one_weekend/mod.rs:59-63, :93-105) are tested ahead of the traversal instead of sitting
     in the BVH; the checker still finds every primitive exactly once.  The book-2 final scene has no
-    such outliers (its largest item is 4x the median) and keeps everything in the tree."""
+    such outliers (its largest item is 4x the median); its front run is what its two grids leave over
+    (seven primitives, tests/test_grid.py), and without grids everything stays in the tree."""
     s = R.BookScene("in_one_weekend", overrides=dict(image_width=64))
     front = R.flatten_check(s.desc)
     monkeypatch.setenv("RRT_NO_FRONT", "1")
@@ -136,7 +137,10 @@ def test_outsized_primitives_leave_the_tree(monkeypatch):
     a = R.flatten_check(s9.desc)
     monkeypatch.setenv("RRT_NO_FRONT", "1")
     b = R.flatten_check(s9.desc)
-    assert a == b
+    assert a["n_nodes"] == b["n_nodes"] - 7 and a["n_prims"] == b["n_prims"]
+    monkeypatch.delenv("RRT_NO_FRONT")
+    monkeypatch.setenv("RRT_NO_GRID", "1")
+    assert R.flatten_check(s9.desc) == b
 
 
 def test_flattener_rejects_malformed_descriptions():

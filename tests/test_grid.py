@@ -40,20 +40,37 @@ def random_spheres(seed, n, moving=False, spread=6.0):
 
 
 # ---- CPU tier --------------------------------------------------------------------------------------
-def test_grid_is_laid_over_even_sphere_fields_only(monkeypatch):
+def test_grid_is_laid_over_even_fields_only(monkeypatch):
     for book, no, want in [("in_one_weekend", None, True), ("in_one_weekend_gpu", None, True), ("the_next_week", 1, True),
-                           ("the_next_week", 2, False), ("the_next_week", 7, False), ("the_next_week", 9, False),
+                           ("the_next_week", 2, False), ("the_next_week", 7, False), ("the_next_week", 8, False),
                            ("the_rest_of_your_life", None, False)]:
         s = R.BookScene(book, no, overrides=dict(image_width=64))
-        g = R.flatten_grid(s.desc)
+        g = R.flatten_grid(s.desc, 0)
         assert (g["res"] != (0, 0, 0)) == want, (book, no, g)
+        assert R.flatten_grid(s.desc, 1)["res"] == (0, 0, 0)
         if want:
             n = R.flatten_check(s.desc)["n_prims"]       # the check walks the cell tables too
             assert g["res"][1] == 1                      # a field on the ground: one cell thick
+            assert g["n_items"] == n - 4                 # everything but the ground and the three large spheres (front run)
             assert g["n_refs"] <= 4 * n and g["max_per_cell"] <= 12
     s = R.BookScene("in_one_weekend", None, overrides=dict(image_width=64))
     monkeypatch.setenv("RRT_NO_GRID", "1")
     assert R.flatten_grid(s.desc)["res"] == (0, 0, 0)
+
+
+def test_book2_final_scene_is_two_grids_and_a_front_run(monkeypatch):
+    """the_next_week/mod.rs:297-401: 400 ground boxes that tile a 20 x 20 lattice (one box per cell), the cluster of
+    1 000 spheres of radius 10, and seven other primitives, which all fit the front run — no tree left to walk."""
+    s = R.BookScene("the_next_week", 9, overrides=dict(image_width=64))
+    boxes, spheres = R.flatten_grid(s.desc, 1), R.flatten_grid(s.desc, 0)
+    assert boxes["res"] == (20, 1, 20) and boxes["n_items"] == 400 and boxes["n_refs"] == 400 and boxes["max_per_cell"] == 1
+    assert spheres["n_items"] == 1000 and min(spheres["res"]) >= 4
+    c = R.flatten_check(s.desc)
+    assert c["n_prims"] == 400 * 6 + 1000 + 7
+    monkeypatch.setenv("RRT_GRID_NO_TILING", "1")        # the same boxes in a padded grid: several per cell
+    padded = R.flatten_grid(s.desc, 1)
+    assert padded["n_items"] == 400 and padded["max_per_cell"] > 1
+    R.flatten_check(s.desc)
 
 
 @pytest.mark.parametrize("seed", range(6))
@@ -74,8 +91,10 @@ def test_small_or_mixed_trees_keep_the_bvh():
     m = b.lambertian((0.5, 0.5, 0.5))
     items = [b.sphere((float(x), 0.2, float(z)), 0.2, m) for x in range(-6, 6) for z in range(-6, 6)]
     assert R.flatten_grid(b.desc(b.list(items)))["res"][1] == 1
-    items.append(b.quad((-1.0, 0.5, -1.0), (2.0, 0.0, 0.0), (0.0, 0.0, 2.0), m))   # one quad in the tree: no grid
+    for k in range(16):   # sixteen quads next to the field: more than the front run holds, so the tree stays
+        items.append(b.quad((-1.0 + k, 0.5, -1.0), (0.5, 0.0, 0.0), (0.0, 0.0, 0.5), m))
     assert R.flatten_grid(b.desc(b.list(items)))["res"] == (0, 0, 0)
+    R.flatten_check(b.desc(b.list(items)))
 
 
 # ---- GPU tier --------------------------------------------------------------------------------------
@@ -110,6 +129,18 @@ def test_grid_and_tree_render_the_same_frame_bit_for_bit(book, scene_no, monkeyp
     (ids, t, a), (pids, pt, b) = _both(s.desc, s.camera, s.integrator, monkeypatch)
     assert np.array_equal(ids, pids) and np.array_equal(t, pt)
     assert np.array_equal(a, b)
+
+
+@pytest.mark.gpu
+def test_book2_final_scene_grids_match_the_tree(monkeypatch):
+    """Boxes that tile their lattice are listed in their own cell only, so a ray within f32 rounding of a vertical box
+    edge may be settled the other way round than by the tree: identical frames up to such pixels (none expected at
+    this size), identical sample counts."""
+    s = R.BookScene("the_next_week", 9, overrides=dict(image_width=200, samples_per_pixel=16, max_depth=12))
+    (ids, t, a), (pids, pt, b) = _both(s.desc, s.camera, s.integrator, monkeypatch)
+    assert (ids != pids).mean() <= 1e-4 and (t != pt).mean() <= 1e-4
+    assert np.array_equal(a[..., 3], b[..., 3])
+    assert (np.abs(a[..., :3] - b[..., :3]).max(axis=2) > 1e-6 * np.maximum(b[..., :3].max(axis=2), 1e-3)).mean() <= 1e-3
 
 
 @pytest.mark.gpu
