@@ -61,6 +61,7 @@ extern "C" {
     pub fn rrt_flatten_check(desc: *const RrtSceneDesc, n_prims: *mut i32, n_nodes: *mut i32, bvh_depth: *mut i32,
                              n_media: *mut i32, n_lights: *mut i32) -> c_int;
     pub fn rrt_scene_features(desc: *const RrtSceneDesc, features: *mut i32) -> c_int;
+    pub fn rrt_flatten_rects(desc: *const RrtSceneDesc, n3: *mut i32) -> c_int;
     pub fn rrt_flatten_grid(desc: *const RrtSceneDesc, kind: c_int, res3: *mut i32, n_items: *mut i32, n_refs: *mut i32, max_per_cell: *mut i32) -> c_int;
     pub fn rrt_philox_kat(c0: u32, c1: u32, c2: u32, c3: u32, k0: u32, k1: u32, out4: *mut u32);
     pub fn rrt_philox_kat_rounds(rounds: c_int, c0: u32, c1: u32, c2: u32, c3: u32, k0: u32, k1: u32, out4: *mut u32) -> c_int;

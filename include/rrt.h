@@ -170,11 +170,12 @@ typedef struct rrt_stats {
   int32_t sm_count;
   int32_t kernel_features; /* feature set of the render-kernel instance the last call ran: bit 0 moving
                             * spheres, 1 quads, 2 constant media, 3 non-solid textures, 4 Perlin noise,
-                            * 5 box leaves (63 = the general instance); a scene runs on the smallest instance covering it.
-                            * RRT_KERNEL=full in the environment at rrt_init forces 63 (debugging). */
+                            * 5 box leaves (63 = the general instance), 6 the scene is walked through grids instead of a tree;
+                            * a scene runs on the smallest instance covering it.
+                            * RRT_KERNEL=full in the environment at rrt_init forces the general instance (debugging). */
   int32_t n_devices;       /* GPUs behind the last call: 1, the size of an rrt_init_multi group, or the communicator's world */
-  int32_t n_grid_cells;    /* cells of the uniform grid the scene's sphere field is walked through, or 0: the BVH
-                            * (an even field of spheres gets a grid next to its BVH; RRT_NO_GRID=1 at rrt_scene_create keeps the BVH) */
+  int32_t n_grid_cells;    /* cells of the uniform grids the scene's even fields of spheres / boxes are walked through, or 0:
+                            * the BVH (RRT_NO_GRID=1 at rrt_scene_create keeps the BVH for every scene) */
   double exchange_ms;      /* device time of the frame exchange after the kernels (NCCL reduce, or gather of owned tiles
                             * + scatter into the frame) on the rank that receives it; 0 on one GPU.  With several GPUs
                             * kernel_ms is the slowest member's kernel and paths counts every member's. */
@@ -193,6 +194,7 @@ typedef struct rrt_scene rrt_scene;
  *   RRT_NO_BOX_LEAVES=1    (rrt_scene_create) axis-aligned boxes stay six separate quad leaves
  *   RRT_NO_FRONT=1         (rrt_scene_create) outsized primitives (a ground sphere) stay in the BVH instead of
  *                          being tested ahead of the traversal
+ *   RRT_NO_RECT_QUADS=1    (rrt_scene_create) axis-aligned rectangles of a root leaf are tested like any other quad
  *   RRT_NO_GRID=1          (rrt_scene_create) an even field of spheres is walked through its BVH, not its grid
  *   RRT_FORCE_GRID=1       (rrt_scene_create) a grid for every sphere-only tree, however uneven */
 int rrt_init(int device, rrt_ctx** out);
@@ -319,6 +321,9 @@ int rrt_scene_features(const rrt_scene_desc* desc, int32_t* features);
 /*   rrt_flatten_grid: the uniform grid the flattener lays over an even field of equal spheres (kind 0) or
  *   axis-aligned boxes (kind 1) (rrt_stats.n_grid_cells): cells per axis (0, 0, 0: no such grid — without any grid
  *   the scene is walked through its BVH), items in it, references in all cells, most in one cell. */
+/*   rrt_flatten_rects: how many quads of a brute-force root leaf (scenes of at most 16 primitives: the Cornell
+ *   boxes) are axis-aligned rectangles with their normal along x, y, z — they get a test of their own. */
+int rrt_flatten_rects(const rrt_scene_desc* desc, int32_t n3[3]);
 int rrt_flatten_grid(const rrt_scene_desc* desc, int kind, int32_t res3[3], int32_t* n_items, int32_t* n_refs,
                      int32_t* max_per_cell);
 void rrt_philox_kat(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1,

@@ -5,8 +5,8 @@ surface -> librrt_host.so, bin/rrt), and this thin ctypes layer.  Importing the 
 load the libraries; the first call does, and fails loudly if they are missing.
 """
 from . import _ffi
-from .api import (BookScene, Context, DescBuilder, GpuScene, RrtError, copy_camera, flatten_check, flatten_grid,
+from .api import (BookScene, Context, DescBuilder, GpuScene, RrtError, copy_camera, flatten_check, flatten_grid, flatten_rects,
                   make_camera, make_overrides, scene_features, shard_plan, shipped_overrides, tile_scatter_host)
 
 __all__ = ["BookScene", "Context", "DescBuilder", "GpuScene", "RrtError", "copy_camera",
-           "flatten_check", "flatten_grid", "make_camera", "make_overrides", "scene_features", "shard_plan", "shipped_overrides", "tile_scatter_host", "_ffi"]
+           "flatten_check", "flatten_grid", "flatten_rects", "make_camera", "make_overrides", "scene_features", "shard_plan", "shipped_overrides", "tile_scatter_host", "_ffi"]

@@ -201,6 +201,13 @@ def flatten_check(desc):
     return dict(zip(("n_prims", "n_nodes", "bvh_depth", "n_media", "n_lights"), [x.value for x in v]))
 
 
+def flatten_rects(desc):
+    """Host-only: (nx, ny, nz) axis-aligned rectangles of a brute-force root leaf."""
+    n = (F.c_int * 3)()
+    _check(F.rrt().rrt_flatten_rects(C.byref(desc), C.byref(n)))
+    return tuple(n)
+
+
 def flatten_grid(desc, kind=0):
     """Host-only: the uniform grid the flattener chose for the scene's field of spheres (kind 0) or boxes (kind 1);
     res (0, 0, 0): none."""

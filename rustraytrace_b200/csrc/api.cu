@@ -71,7 +71,7 @@ int rrt::scene_upload(rrt_ctx* c, const FlatScene& F, rrt_scene** out) {
   int rc = RRT_OK;
   if ((rc = upload(sc, F.prims, &D.prims)) || (rc = upload(sc, F.prims64, &D.prims64)) ||
       (rc = upload(sc, F.nodes, &D.nodes)) || (rc = upload(sc, F.bprims, &D.bprims)) ||
-      (rc = upload(sc, F.boxes, &D.boxes)) || (rc = upload(sc, F.qpairs, &D.qpairs)) || (rc = upload(sc, F.nodes4, &D.nodes4)) ||
+      (rc = upload(sc, F.boxes, &D.boxes)) || (rc = upload(sc, F.qpairs, &D.qpairs)) || (rc = upload(sc, F.rects, &D.rects)) || (rc = upload(sc, F.nodes4, &D.nodes4)) ||
       (rc = upload(sc, F.materials, &D.materials)) || (rc = upload(sc, F.textures, &D.textures)) ||
       (rc = upload(sc, F.images, &D.images)) || (rc = upload(sc, F.texels, &texels)) ||
       (rc = upload(sc, F.perlins, &D.perlins)) || (rc = upload(sc, F.media, &D.media)) ||
@@ -88,6 +88,7 @@ int rrt::scene_upload(rrt_ctx* c, const FlatScene& F, rrt_scene** out) {
   D.n_lights = (int)F.lights.size();
   D.has_motion = F.has_motion;
   D.features = F.features;
+  for (int a = 0; a < 3; ++a) D.n_rects[a] = F.n_rects[a];
   D.n_grids = 0;
   for (size_t g = 0; g < F.grids.size() && g < RRT_MAX_GRIDS; ++g) { D.grids[g] = F.grids[g]; D.n_grids += F.grids[g].n_items > 0; }
   sc->n_nodes = D.n_nodes; sc->n_prims = D.n_prims; sc->n_media = D.n_media; sc->n_lights = D.n_lights;
@@ -657,6 +658,15 @@ extern "C" int rrt_flatten_grid(const rrt_scene_desc* desc, int kind, int32_t re
   return RRT_OK;
 }
 
+extern "C" int rrt_flatten_rects(const rrt_scene_desc* desc, int32_t n3[3]) {
+  FlatScene F;
+  std::string err;
+  int st = flatten_scene(desc, F, err);
+  if (st != RRT_OK) return fail(st, "scene flatten failed: " + err);
+  if (n3) for (int a = 0; a < 3; ++a) n3[a] = F.n_rects[a];
+  return RRT_OK;
+}
+
 extern "C" int rrt_flatten_check(const rrt_scene_desc* desc, int32_t* n_prims, int32_t* n_nodes, int32_t* bvh_depth,
                                  int32_t* n_media, int32_t* n_lights) {
   FlatScene F;
@@ -710,6 +720,23 @@ extern "C" int rrt_flatten_check(const rrt_scene_desc* desc, int32_t* n_prims, i
   }
   for (int i = 0; i < F.n_prims; ++i)
     if (seen[i] != 1) return fail(RRT_ERR_INVALID, "flatten check: primitive not in exactly one leaf");
+  // rectangles of a root leaf: its first quads, each record on the plane of its quad
+  {
+    const int nr = F.n_rects[0] + F.n_rects[1] + F.n_rects[2];
+    if (nr > 0) {
+      const int leaf = ~F.root_ref, first = (leaf >> 8) + ((leaf >> 4) & 15), nq = leaf & 15;
+      if (F.root_ref >= 0 || nr > nq || (int)F.rects.size() != 2 * nr) return fail(RRT_ERR_INVALID, "flatten check: rectangle records do not match the root leaf");
+      int k = 0;
+      for (int a = 0; a < 3; ++a)
+        for (int j = 0; j < F.n_rects[a]; ++j, ++k) {
+          const float4 p0 = F.prims[4 * (first + k)];
+          const float n[3] = {p0.x, p0.y, p0.z};
+          const bool axis_ok = std::fabs(std::fabs(n[a]) - 1.0f) < 1e-6f && n[(a + 1) % 3] == 0.0f && n[(a + 2) % 3] == 0.0f;
+          if (!axis_ok || std::fabs(n[a] * p0.w - F.rects[2 * k].x) > 1e-5f * (1.0f + std::fabs(p0.w)))
+            return fail(RRT_ERR_INVALID, "flatten check: rectangle record off its quad's plane");
+        }
+    }
+  }
   // grids: every reference in range, every item referenced from every cell its bounds overlap (so that a walk
   // through the cells cannot miss it), and — the render kernel walks no tree then — every primitive outside
   // the front run in exactly one grid

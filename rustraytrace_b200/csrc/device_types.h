@@ -84,7 +84,12 @@ enum SceneFeature {
   SF_TEXTURES = 8,  // a material whose texture is not a solid colour (checker / image / noise)
   SF_NOISE = 16,    // a Perlin noise texture: its turbulence loop alone costs 16 registers (80 instead of 64)
   SF_BOXES = 32,    // box leaves: the six quads of an axis-aligned box_() behind one slab test
-  SF_ALL = 63
+  SF_ALL = 63,
+  // Not a capability but the way the scene is walked (DevScene::grids): even fields in uniform grids and the rest in
+  // the front run, no tree.  An instance is compiled for one or the other, so that neither carries the other's code
+  // (the general book-2 instance with both was 75 KB of SASS, and its warps waited for instruction fetches 1.8 times per
+  // issue: profiles/README.md r02l).  A grid scene runs on an instance with this bit, any other on one without.
+  SF_GRID = 64
 };
 
 struct DevMaterial {  // 32 B
@@ -164,7 +169,12 @@ struct DevScene {
   const float4* nodes;
   const float4* bprims;
   const float4* boxes;   // two float4 per box leaf
-  const float4* qpairs;  // quad pair records of a brute-force root leaf, or null
+  const float4* qpairs;  // quad pair records of a brute-force root leaf (its quads that are not in `rects`), or null
+  // Axis-aligned rectangles of a brute-force root leaf (walls, floor, ceiling and light of the Cornell boxes): the leaf's
+  // first n_rects[0] + n_rects[1] + n_rects[2] quads, grouped by the axis a of their normal.  Two float4 each:
+  // (plane coordinate along a, centre along b, centre along c, -) (half extent along b, along c, -, -), b = a+1, c = a+2 mod 3.
+  const float4* rects;
+  int n_rects[3];
   const float4* nodes4;  // experiment (-DRRT_BVH4, profiles/README.md r02): the same tree collapsed to 4-wide nodes,
                          //   8 float4 each: children 0,1 and 2,3 as two slab2 pair records, then the four refs; else null
   const double* prims64;

@@ -53,6 +53,19 @@ struct BoxGroup {
   double lo[3], hi[3];
 };
 
+// Axis of an axis-aligned rectangle (quad whose edges u, v each run along one coordinate axis: the walls, floor,
+// ceiling and light of the Cornell boxes, the_rest_of_your_life/mod.rs:82-130), or -1.
+int rect_axis(const BakedPrim& p) {
+  auto along = [](const D3& e) {
+    const int nz = (e.x != 0.0) + (e.y != 0.0) + (e.z != 0.0);
+    return nz == 1 ? (e.x != 0.0 ? 0 : (e.y != 0.0 ? 1 : 2)) : -1;
+  };
+  if (p.kind != PRIM_QUAD) return -1;
+  const int au = along(p.u), av = along(p.v);
+  if (au < 0 || av < 0 || au == av) return -1;
+  return 3 - au - av;
+}
+
 void pad_axis(double& lo, double& hi) {  // Aabb::pad_to_minimums, aabb.rs:107-118
   const double delta = 0.0001;
   if (hi - lo < delta) { lo -= delta / 2; hi += delta / 2; }
@@ -629,7 +642,16 @@ bool grid_geometry(const std::vector<BakedPrim>& items, const std::vector<int>& 
   // a flat field is one cell thick: an axis no longer than the items themselves gets the items' extent
   double ext[3], vol = 1;
   for (int a = 0; a < 3; ++a) { ext[a] = std::max(G.hi[a] - G.lo[a], std::max(mean_ext[a], 1e-9)); vol *= ext[a]; }
-  const double dens = std::cbrt(lambda * (double)members.size() / vol);
+  // A dense cloud (the 1 000 overlapping spheres of the book-2 final scene fill 40 % of their bounds) stops a ray
+  // within a cell or two, so what counts is how many items a cell lists: four times the cells.  Measured, Mpaths/s
+  // at 500 spp: C4 2 998 / 3 099 / 3 139 at 0.5 / 1 / 2 cells per item, C2 (a sparse layer) 9 831 / 9 727 / 9 539 at 0.35 / 0.5 / 1.
+  double fill = 0;
+  if (!of_boxes) {
+    for (int i : members) fill += 4.18879 * items[i].r * items[i].r * items[i].r;
+    fill /= vol;
+  }
+  const double lambda_eff = (!le && fill > 0.25) ? 4.0 * lambda : lambda;
+  const double dens = std::cbrt(lambda_eff * (double)members.size() / vol);
   // Boxes that tile an axis exactly (the 20 x 20 ground boxes of the book-2 final scene, the_next_week/mod.rs:309-327:
   // equal widths at whole multiples of the width) get cells that ARE the tiles along that axis: one box per cell
   // instead of the nine a padded membership would list.  The walk can then differ from the tree only for a ray that
@@ -683,7 +705,7 @@ bool grid_geometry(const std::vector<BakedPrim>& items, const std::vector<int>& 
     std::fprintf(stderr, "grid candidate: %zu items, %dx%dx%d cells, %.2f references per item, most in a cell %zu\n", members.size(),
                  G.res[0], G.res[1], G.res[2], (double)G.n_refs / (double)members.size(), G.crowded);
   if (G.crowded > 255 || G.n_refs >= (1u << 22)) return false;
-  if (!force && ((double)G.n_refs > 8.0 * (double)members.size() || G.crowded > 64)) return false;   // not an even field
+  if (!force && ((double)G.n_refs > 16.0 * (double)members.size() || G.crowded > 64)) return false;   // not an even field
   return true;
 }
 
@@ -751,6 +773,7 @@ void emit_grids(const std::vector<BakedPrim>& items, const std::vector<int>& ite
   if (!present) { out.grid_cells.clear(); out.grid_refs.clear(); return; }
   if (out.grid_refs.empty()) out.grid_refs.push_back(0);
   out.grids = slots;   // both slots, an absent one has n_items == 0
+  out.features |= SF_GRID;
 }
 
 }  // namespace
@@ -1014,6 +1037,33 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
         // `contains`), so a leaf that tests them in that order with `t <= closest` needs no tie lookup
         // (quad_pairs_hit32 relies on it; quad_hit32's explicit rule agrees with it)
         if (pass == 1) std::stable_sort(run.begin(), run.end(), [&](int a, int b) { return items[a].order < items[b].order; });
+        // Brute-force root leaf: axis-aligned rectangles first, grouped by axis (rect_quads_hit32 tests one in a dozen
+        // instructions), the other quads after them; inside a group the reference's order stays.  Two quads that share
+        // a plane (a box standing on the floor) keep the reference's equal-t rule — the later one wins — as long as
+        // they are tested in that order: not when a rectangle comes after a coplanar quad that is none.
+        if (pass == 1 && single && !std::getenv("RRT_NO_RECT_QUADS")) {
+          bool coplanar = false;   // ... in the one order the grouping would reverse
+          for (size_t x = 0; x < run.size() && !coplanar; ++x)
+            for (size_t y = x + 1; y < run.size() && !coplanar; ++y) {
+              const BakedPrim& A = items[run[x]]; const BakedPrim& Bq = items[run[y]];   // A before Bq in the reference
+              const double c = dot(A.n, Bq.n), scale = 1.0 + std::fabs(A.d) + std::fabs(Bq.d);
+              const bool same_plane = std::fabs(std::fabs(c) - 1.0) < 1e-12 && std::fabs(A.d - (c > 0 ? Bq.d : -Bq.d)) < 1e-9 * scale;
+              if (same_plane && rect_axis(A) < 0 && rect_axis(Bq) >= 0) coplanar = true;
+            }
+          if (!coplanar) {
+            std::stable_sort(run.begin(), run.end(), [&](int a, int b) { return (unsigned)rect_axis(items[a]) < (unsigned)rect_axis(items[b]); });
+            for (int i : run) {
+              const int ax = rect_axis(items[i]);
+              if (ax < 0) break;
+              const BakedPrim& q = items[i];
+              const int b = (ax + 1) % 3, c = (ax + 2) % 3;
+              const double e_b = q.u[b] + q.v[b], e_c = q.u[c] + q.v[c];   // one of u, v runs along b, the other along c
+              out.rects.push_back(f4(q.Q[ax], q.Q[b] + 0.5 * e_b, q.Q[c] + 0.5 * e_c, 0));
+              out.rects.push_back(f4(0.5 * std::fabs(e_b), 0.5 * std::fabs(e_c), 0, 0));
+              out.n_rects[ax]++;
+            }
+          }
+        }
         for (int i : run) { item_flat[i] = (int)(out.prims.size() / 4); emit_prim32(items[i], out.prims); emit_prim64(items[i], out.prims64); (pass == 0 ? s : q)++; }
       }
       leaf_ref[li] = make_leaf_ref(emitted, s, q);
@@ -1026,8 +1076,9 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
     // quad_pairs_hit32 (device_types.h); an odd count is padded with a quad of normal 0, which the
     // |denom| >= 1e-8 test of quad.rs:67 rejects.
     const int leaf = ~out.root_ref, first = leaf >> 8, ns = (leaf >> 4) & 15, nq = leaf & 15;
+    const int n_rect = out.n_rects[0] + out.n_rects[1] + out.n_rects[2];   // the first n_rect quads are rectangles (out.rects)
     if ((leaf & 0xFF) != LEAF_BOX_MARK && nq > 0 && !std::getenv("RRT_NO_QUAD_PAIRS")) {
-      for (int k = 0; k < nq; k += 2) {
+      for (int k = n_rect; k < nq; k += 2) {
         float4 a[3], b[3];
         for (int j = 0; j < 3; ++j) {
           a[j] = out.prims[4 * (first + ns + k) + j];

@@ -18,6 +18,8 @@ struct FlatScene {
   std::vector<float4> nodes;      // 4 per inner node
   std::vector<float4> nodes4;     // -DRRT_BVH4 experiment only: 8 per 4-wide node
   std::vector<float4> qpairs;     // root-leaf quads again, 6 float4 per pair (device_types.h)
+  std::vector<float4> rects;      // axis-aligned rectangles of a root leaf, 2 float4 each (device_types.h)
+  int n_rects[3] = {0, 0, 0};     // how many with normal x, y, z: the first quads of the root leaf, in that order
   std::vector<unsigned> grid_cells;  // uniform grids over even fields of spheres / boxes (device_types.h DevScene), pooled; or empty
   std::vector<int> grid_refs;
   std::vector<DevGrid> grids;        // at most RRT_MAX_GRIDS

@@ -142,6 +142,9 @@ __device__ inline void box_leaf_hit32(const float4* __restrict__ prims, const fl
       if (h.prim == (face | PRIM_QUAD_BIT)) return;
     }
   }
+#ifndef RRT_BOX_UNROLL
+#pragma unroll 1   // the rare path (origin inside the box, grazing an edge): one copy of the quad test
+#endif
   for (int f = 0; f < 6; ++f) quad_hit32(prims, first + f, r, tmin, skip, h);
 }
 
@@ -232,8 +235,28 @@ __device__ __forceinline__ void quad_pairs_hit32(const float4* __restrict__ prim
   }
 }
 
-// The brute-force root leaf (scenes of at most RRT_SINGLE_LEAF_MAX primitives): spheres one by one,
-// quads as pairs when the flattener supplied pair records.
+// Axis-aligned rectangles of a brute-force root leaf (device_types.h DevScene::rects), normal along axis A: Quad::hit
+// (quad.rs:64-91) collapses to t = (plane - o_a) / d_a and two interval tests on the other two coordinates of the hit
+// point — a dozen instructions against 35 for a quad of a pair.  |d_a| < 1e-8 is quad.rs:67's parallel test (the
+// normal is a unit axis), alpha / beta in [0, 1] (quad.rs:51-60) is |p - centre| <= half extent.
+template <int A>
+__device__ __forceinline__ void rect_quads_hit32(const float4* __restrict__ rec, int n, int index, const Ray32& r, float tmin, int skip, Hit32& h) {
+  const float oa = A == 0 ? r.o.x : (A == 1 ? r.o.y : r.o.z), da = A == 0 ? r.d.x : (A == 1 ? r.d.y : r.d.z);
+  const float ob = A == 0 ? r.o.y : (A == 1 ? r.o.z : r.o.x), db = A == 0 ? r.d.y : (A == 1 ? r.d.z : r.d.x);
+  const float oc = A == 0 ? r.o.z : (A == 1 ? r.o.x : r.o.y), dc = A == 0 ? r.d.z : (A == 1 ? r.d.x : r.d.y);
+  const float ida = 1.0f / da;
+  const bool steep = fabsf(da) >= 1e-8f;
+  for (int k = 0; k < n; ++k, ++index) {
+    const float4 r0 = ldg4(rec + 2 * k), r1 = ldg4(rec + 2 * k + 1);
+    const float t = (r0.x - oa) * ida;
+    const float pb = fmaf(t, db, ob), pc = fmaf(t, dc, oc);
+    const bool ok = steep & (t >= tmin) & (t <= h.t) & (fabsf(pb - r0.y) <= r1.x) & (fabsf(pc - r0.z) <= r1.y) & (index != skip);
+    if (ok) { h.t = t; h.prim = index | PRIM_QUAD_BIT; }
+  }
+}
+
+// The brute-force root leaf (scenes of at most RRT_SINGLE_LEAF_MAX primitives): spheres one by one, axis-aligned
+// rectangles by their own test, the other quads as pairs when the flattener supplied pair records.
 template <int FEAT>
 __device__ __forceinline__ void root_leaf_hit32(const DevScene& S, int leaf, const Ray32& r, float a, float inv_a, float tmin,
                                                 int skip, bool motion, Hit32& h) {
@@ -243,8 +266,17 @@ __device__ __forceinline__ void root_leaf_hit32(const DevScene& S, int leaf, con
   if (FEAT & SF_QUADS) {
     // not in the instances with box leaves (the book-2 final scene): a scene with box leaves has a tree, and
     // those instances sit at their register limit
-    if (!(FEAT & SF_BOXES) && S.qpairs) quad_pairs_hit32(S.prims, S.qpairs, first, nq, r, tmin, skip, h);
-    else for (int k = 0; k < nq; ++k) quad_hit32(S.prims, first + k, r, tmin, skip, h);
+    if (!(FEAT & SF_BOXES)) {
+      if (S.rects) {   // the leaf's first quads, grouped by the axis of their normal
+        const int nx = S.n_rects[0], ny = S.n_rects[1], nz = S.n_rects[2];
+        if (nx > 0) rect_quads_hit32<0>(S.rects, nx, first, r, tmin, skip, h);
+        if (ny > 0) rect_quads_hit32<1>(S.rects + 2 * nx, ny, first + nx, r, tmin, skip, h);
+        if (nz > 0) rect_quads_hit32<2>(S.rects + 2 * (nx + ny), nz, first + nx + ny, r, tmin, skip, h);
+        first += nx + ny + nz; nq -= nx + ny + nz;
+      }
+      if (S.qpairs) { quad_pairs_hit32(S.prims, S.qpairs, first, nq, r, tmin, skip, h); nq = 0; }
+    }
+    for (int k = 0; k < nq; ++k) quad_hit32(S.prims, first + k, r, tmin, skip, h);
   }
 }
 
@@ -290,6 +322,9 @@ __device__ __forceinline__ void grid_hit32(const DevScene& S, const DevGrid& G, 
     const unsigned hdr = __ldg(S.grid_cells + cell);
     const int* refs = S.grid_refs + (hdr >> 8);
     const int cnt = (int)(hdr & 255u);
+#ifndef RRT_GRID_UNROLL
+#pragma unroll 1   // few lanes are in the same cell loop together: copies of the test only cost instruction cache
+#endif
     for (int k = 0; k < cnt; ++k) {
       if (KIND == 0) sphere_hit32(S.prims, __ldg(refs + k), r, a, inv_a, tmin, skip, motion, h);
       else box_leaf_hit32(S.prims, S.boxes, __ldg(refs + k), r, V3f(idx, idy, idz), tmin, skip, h);
@@ -311,6 +346,13 @@ __device__ inline void world_hit32(const DevScene& S, const Ray32& r, float tmin
   const float a = dot(r.d, r.d);
   const float inv_a = 1.0f / a;
   const bool motion = (FEAT & SF_MOTION) && S.has_motion != 0;
+  if (FEAT & SF_GRID) {   // even fields in grids, everything else in the front run: no tree to walk (device_types.h SF_GRID)
+    if (S.front_ref != -1) leaf_hit32<FEAT>(S.prims, S.boxes, ~S.front_ref, r, V3f(0.0f, 0.0f, 0.0f), a, inv_a, tmin, skip, motion, h);
+    const float gx = safe_rcp(r.d.x), gy = safe_rcp(r.d.y), gz = safe_rcp(r.d.z);
+    if (S.grids[0].n_items > 0) grid_hit32<FEAT, 0>(S, S.grids[0], r, gx, gy, gz, a, inv_a, tmin, skip, motion, h);
+    if ((FEAT & SF_BOXES) && S.grids[1].n_items > 0) grid_hit32<FEAT, 1>(S, S.grids[1], r, gx, gy, gz, a, inv_a, tmin, skip, motion, h);
+    return;
+  }
   int cur = S.root_ref;
   if (cur < 0) {  // the whole scene is one leaf: brute force, uniform control flow (a root leaf is never a box leaf)
     root_leaf_hit32<FEAT>(S, ~cur, r, a, inv_a, tmin, skip, motion, h);
@@ -319,11 +361,6 @@ __device__ inline void world_hit32(const DevScene& S, const Ray32& r, float tmin
   // front run (flatten.cpp): primitives spanning most of the scene, tested by all lanes together
   if (S.front_ref != -1) leaf_hit32<FEAT>(S.prims, S.boxes, ~S.front_ref, r, V3f(0.0f, 0.0f, 0.0f), a, inv_a, tmin, skip, motion, h);
   const float idx = safe_rcp(r.d.x), idy = safe_rcp(r.d.y), idz = safe_rcp(r.d.z);
-  if (S.n_grids > 0) {   // even fields in grids, the rest in the front run above: no tree to walk
-    if (S.grids[0].n_items > 0) grid_hit32<FEAT, 0>(S, S.grids[0], r, idx, idy, idz, a, inv_a, tmin, skip, motion, h);
-    if ((FEAT & SF_BOXES) && S.grids[1].n_items > 0) grid_hit32<FEAT, 1>(S, S.grids[1], r, idx, idy, idz, a, inv_a, tmin, skip, motion, h);
-    return;
-  }
   float oodx = r.o.x * idx, oody = r.o.y * idy, oodz = r.o.z * idz;
   asm("" : "+f"(oodx), "+f"(oody), "+f"(oodz));  // opaque: keep in registers, do not rematerialise in the loop
   int stack[RRT_STACK];

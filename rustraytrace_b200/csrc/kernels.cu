@@ -28,7 +28,8 @@ __global__ void probe_kernel32(const __grid_constant__ ProbeArgs A) {
   r.d = V3f(C.p00x + fx * C.dux + fy * C.dvx, C.p00y + fx * C.duy + fy * C.dvy, C.p00z + fx * C.duz + fy * C.dvz);
   r.tm = 0.0f;
   Hit32 h; h.t = CUDART_INF_F; h.prim = -1;
-  world_hit32<SF_ALL>(A.S, r, 0.001f, -1, h);
+  if (A.S.n_grids > 0) world_hit32<SF_ALL | SF_GRID>(A.S, r, 0.001f, -1, h);
+  else world_hit32<SF_ALL>(A.S, r, 0.001f, -1, h);
   int id = -1;
   if (h.prim >= 0) {
     int idx = h.prim & ~PRIM_QUAD_BIT;
@@ -126,10 +127,15 @@ const RenderVariant* select_render_variant(int integrator, int features, bool fo
   int n = 0;
   const RenderVariant* t = integrator == RRT_INT_BOOK1 ? render_variants_book1(&n)
                          : integrator == RRT_INT_BOOK2 ? render_variants_book2(&n) : render_variants_book3(&n);
-  if (!force_full)
-    for (int i = 0; i < n; ++i)
-      if ((t[i].features & features) == features) return &t[i];
-  return &t[n - 1];  // SF_ALL is the last entry of every table
+  // the way the scene is walked (SF_GRID) must match; among those instances the first that covers the scene, or —
+  // force_full — the general one, which is the last of its kind in every table
+  const RenderVariant* general = nullptr;
+  for (int i = 0; i < n; ++i) {
+    if ((t[i].features & SF_GRID) != (features & SF_GRID)) continue;
+    if (!force_full && (t[i].features & features) == features) return &t[i];
+    general = &t[i];
+  }
+  return general;
 }
 
 static const void* render_entry(const RenderVariant* v, int schedule) {

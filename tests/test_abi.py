@@ -89,15 +89,15 @@ def test_scene_feature_bits_select_the_kernel_instance():
     def feat(book, no=None):
         s = R.BookScene(book, no, overrides=dict(image_width=64))
         return R.scene_features(s.desc)
-    assert feat("in_one_weekend") == 0                      # static spheres, solid colours
-    assert feat("the_next_week", 1) == F.SF_MOTION | F.SF_TEXTURES   # bouncing spheres on a checker ground
+    assert feat("in_one_weekend") == F.SF_GRID              # a field of spheres: walked through a grid, no tree
+    assert feat("the_next_week", 1) == F.SF_GRID | F.SF_MOTION | F.SF_TEXTURES   # bouncing spheres on a checker ground
     assert feat("the_next_week", 3) == F.SF_TEXTURES        # earth (image texture)
     assert feat("the_next_week", 4) == F.SF_TEXTURES | F.SF_NOISE   # perlin
     assert feat("the_next_week", 6) == F.SF_QUADS | F.SF_TEXTURES | F.SF_NOISE   # simple light over perlin spheres
     assert feat("the_next_week", 5) == F.SF_QUADS
     assert feat("the_next_week", 7) == F.SF_QUADS           # cornell box
     assert feat("the_next_week", 8) == F.SF_QUADS | F.SF_MEDIA   # cornell smoke
-    assert feat("the_next_week", 9) == F.SF_ALL             # final scene
+    assert feat("the_next_week", 9) == F.SF_ALL | F.SF_GRID   # final scene: every feature, two grids
     assert feat("the_rest_of_your_life") == F.SF_QUADS      # cornell box + glass sphere
 
 

@@ -170,12 +170,12 @@ def test_teardown_in_either_order_is_safe():
 
 
 @pytest.mark.parametrize("book,scene_no,feat", [
-    ("in_one_weekend", None, 0), ("the_next_week", 1, F.SF_MOTION | F.SF_TEXTURES), ("the_next_week", 3, F.SF_TEXTURES), ("the_next_week", 4, F.SF_TEXTURES | F.SF_NOISE),
+    ("in_one_weekend", None, F.SF_GRID), ("the_next_week", 1, F.SF_GRID | F.SF_MOTION | F.SF_TEXTURES), ("the_next_week", 3, F.SF_TEXTURES), ("the_next_week", 4, F.SF_TEXTURES | F.SF_NOISE),
     ("the_next_week", 5, F.SF_QUADS), ("the_next_week", 6, F.SF_QUADS | F.SF_TEXTURES | F.SF_NOISE),
-    ("the_next_week", 8, F.SF_QUADS | F.SF_MEDIA), ("the_next_week", 9, F.SF_ALL), ("the_rest_of_your_life", None, F.SF_QUADS)])
+    ("the_next_week", 8, F.SF_QUADS | F.SF_MEDIA), ("the_next_week", 9, F.SF_ALL | F.SF_GRID), ("the_rest_of_your_life", None, F.SF_QUADS)])
 def test_specialised_kernel_instance_equals_the_general_one(ctx, book, scene_no, feat, monkeypatch):
     """A scene runs on the smallest render_kernel<INTEGRATOR, FEAT> covering it; RRT_KERNEL=full forces
-    the SF_ALL instance.  Same seed, same Philox keys: the two frames agree up to the compiler's
+    the SF_ALL instance (of the same traversal: SF_GRID stays as the scene has it).  Same seed, same Philox keys: the two frames agree up to the compiler's
     different FMA contraction in the two instances (a handful of paths that flip at a boundary)."""
     s = R.BookScene(book, scene_no, overrides=dict(image_width=96, samples_per_pixel=64, max_depth=12))
     gs = ctx.scene(s.desc)
@@ -186,7 +186,7 @@ def test_specialised_kernel_instance_equals_the_general_one(ctx, book, scene_no,
     monkeypatch.delenv("RRT_KERNEL")
     gf = full.scene(s.desc)
     b = full.render(gf, s.camera, s.integrator, seed=5).astype(np.float64)
-    assert full.stats()["kernel_features"] == F.SF_ALL
+    assert full.stats()["kernel_features"] == F.SF_ALL | (feat & F.SF_GRID)
     gf.close(); full.close(); gs.close()
     assert np.array_equal(a[..., 3], b[..., 3])
     ma, mb = a[..., :3].mean(axis=(0, 1)), b[..., :3].mean(axis=(0, 1))
