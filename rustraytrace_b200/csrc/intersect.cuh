@@ -154,10 +154,17 @@ __device__ inline void leaf_hit32(const float4* __restrict__ prims, const float4
                                   const Ray32& r, V3f id, float a, float inv_a, float tmin, int skip, bool motion, Hit32& h) {
   if ((FEAT & SF_BOXES) && (leaf & 0xFF) == LEAF_BOX_MARK) { box_leaf_hit32(prims, boxes, leaf >> 8, r, id, tmin, skip, h); return; }
   int first = leaf >> 8, ns = (leaf >> 4) & 15, nq = leaf & 15;
+#ifdef RRT_FRONT_UNROLL1
+#pragma unroll 1
+#endif
   for (int k = 0; k < ns; ++k) sphere_hit32(prims, first + k, r, a, inv_a, tmin, skip, motion, h);
   first += ns;
-  if (FEAT & SF_QUADS)
+  if (FEAT & SF_QUADS) {
+#ifdef RRT_FRONT_UNROLL1
+#pragma unroll 1
+#endif
     for (int k = 0; k < nq; ++k) quad_hit32(prims, first + k, r, tmin, skip, h);
+  }
 }
 
 

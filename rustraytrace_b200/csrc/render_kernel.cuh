@@ -368,6 +368,7 @@ render_kernel(const __grid_constant__ RenderArgs A) {
         int s_new = s1;
         if (STEAL) {
           int tries = 0;
+#pragma unroll 1   // (unrolled, the shared-memory atomic and its warp aggregation were a fifth of the book-1 instance)
           for (; tries < 32; ++tries) {
             s_new = atomicAdd(&sh_next[wbase + tgt], 1);
             if (s_new < s1) break;
