@@ -368,7 +368,9 @@ render_kernel(const __grid_constant__ RenderArgs A) {
         int s_new = s1;
         if (STEAL) {
           int tries = 0;
-#pragma unroll 1   // (unrolled, the shared-memory atomic and its warp aggregation were a fifth of the book-1 instance)
+          // (ptxas unrolls this four times, 199 instructions.  Do not roll it up: with `#pragma unroll 1` the lanes
+          // leave the loop at different trips and no longer re-converge before the trace — C2 -24 %, C5 3.5x slower,
+          // profiles/README.md r02o)
           for (; tries < 32; ++tries) {
             s_new = atomicAdd(&sh_next[wbase + tgt], 1);
             if (s_new < s1) break;
