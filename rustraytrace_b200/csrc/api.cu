@@ -373,12 +373,12 @@ void rrt_scene_destroy(rrt_scene* sc) {
   delete sc;
 }
 
-int rrt_scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out) {
+static int scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out, bool tree_optional) {
   if (!c || !out) return fail(RRT_ERR_INVALID, "rrt_scene_create: null argument");
   *out = nullptr;
   FlatScene F;
   std::string err;
-  int st = flatten_scene(desc, F, err);
+  int st = flatten_scene(desc, F, err, RRT_SINGLE_LEAF_MAX, 1, tree_optional);
   if (st != RRT_OK) return fail(st, "scene flatten failed: " + err);
   if (F.bvh_depth >= RRT_STACK)   // the traversal stack holds one entry per level (intersect.cuh)
     return fail(RRT_ERR_UNSUPPORTED, "BVH depth " + std::to_string(F.bvh_depth) + " exceeds the traversal stack (" + std::to_string(RRT_STACK) + ")");
@@ -394,6 +394,8 @@ int rrt_scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out) {
   *out = sc;
   return RRT_OK;
 }
+
+int rrt_scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out) { return scene_create(c, desc, out, false); }
 
 int rrt_image_height(const rrt_camera* cam) {
   if (!cam || !(cam->aspect_ratio > 0.0)) return 0;
@@ -439,7 +441,7 @@ int rrt_render(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, const rrt
 int rrt_render_frame(rrt_ctx* c, const rrt_scene_desc* desc, const rrt_camera* cam, const rrt_render_params* p,
                      float* accum_host) {
   rrt_scene* sc = nullptr;
-  int rc = rrt_scene_create(c, desc, &sc);
+  int rc = scene_create(c, desc, &sc, true);   // rendered once and freed: no tree where grids do the walking
   if (rc) return rc;
   rc = rrt_render(c, sc, cam, p, accum_host);
   uint64_t h2d = sc->h2d_bytes;

@@ -778,7 +778,7 @@ void emit_grids(const std::vector<BakedPrim>& items, const std::vector<int>& ite
 
 }  // namespace
 
-int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, int single_leaf_max, int max_leaf) {
+int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, int single_leaf_max, int max_leaf, bool tree_optional) {
   if (!desc) { err = "scene description is null"; return RRT_ERR_INVALID; }
   if (desc->n_hittables < 0 || (desc->n_hittables > 0 && !desc->hittables) ||
       (desc->n_children > 0 && !desc->children) || (desc->n_materials > 0 && !desc->materials) ||
@@ -990,6 +990,11 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
     B.nodes.push_back(BNode());
     B.bounds(0, (int)items.size(), B.nodes[0].lo, B.nodes[0].hi);
     B.nodes[0].first = 0; B.nodes[0].count = (int)items.size();
+  } else if (tree_optional && n_grids_chosen > 0) {
+    // The caller will only render (rrt_render_frame: upload, render, free) and the scene is walked through grids: the
+    // tree would serve the f64 probe alone.  Every item a leaf of its own, in construction order; no inner nodes.
+    for (size_t i = 0; i < items.size(); ++i) { BNode n; n.first = (int)i; n.count = 1; B.nodes.push_back(n); }
+    root = -1;
   } else {
     root = B.build(0, (int)items.size(), 0);
   }
@@ -1069,6 +1074,11 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
       leaf_ref[li] = make_leaf_ref(emitted, s, q);
       emitted += n.count;
     }
+  }
+  if (root < 0) {   // no tree (tree_optional): grids and front run only
+    out.root_ref = 0;
+    emit_grids(items, item_flat, out);
+    return out.grids.empty() ? RRT_ERR_INVALID : RRT_OK;
   }
   if (B.nodes[root].left < 0) {
     out.root_ref = leaf_ref[root];

@@ -45,8 +45,10 @@ struct FlatScene {
 #endif
 // single_leaf_max: scenes with at most this many primitives become one root leaf (brute force).
 // max_leaf: primitives per leaf below the root; the render kernel's traversal loop relies on 1.
+// tree_optional: the caller will never probe the scene — where it is walked through grids no BVH is built (FlatScene::nodes
+// stays empty; rrt_render_frame, 1 ms of host time on the book-1 final scene).
 int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err,
-                  int single_leaf_max = RRT_SINGLE_LEAF_MAX, int max_leaf = 1);
+                  int single_leaf_max = RRT_SINGLE_LEAF_MAX, int max_leaf = 1, bool tree_optional = false);
 
 // Camera::initialize (camera.rs:108-154) -> device camera blocks.  Returns image height.
 int camera_initialize(const rrt_camera* cam, DevCamera& c32, DevCamera64& c64);

@@ -169,3 +169,23 @@ def test_grid_probe_against_the_oracle():
     hit = (oids >= 0) & (ids == oids)
     rel = np.abs(t[hit] - ot[hit]) / ot[hit]
     assert np.percentile(rel, 99) <= 1e-4
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("book,scene_no", [("in_one_weekend", None), ("the_next_week", 9)])
+def test_one_shot_render_without_a_tree_is_the_same_frame(book, scene_no, monkeypatch):
+    """rrt_render_frame uploads, renders and frees: where the scene is walked through grids it builds no BVH at all
+    (flatten_scene tree_optional).  Same primitives, same cells, same frame as the scene handle that has one."""
+    s = R.BookScene(book, scene_no, overrides=dict(image_width=160, samples_per_pixel=16, max_depth=12))
+    monkeypatch.setenv("RRT_DETERMINISTIC", "1")
+    ctx = R.Context(0)
+    monkeypatch.delenv("RRT_DETERMINISTIC")
+    gs = ctx.scene(s.desc)
+    assert ctx.stats()["n_bvh_nodes"] > 0
+    a = ctx.render(gs, s.camera, s.integrator, seed=8)
+    gs.close()
+    b = ctx.render_frame(s.desc, s.camera, s.integrator, seed=8)
+    st = ctx.stats()
+    ctx.close()
+    assert st["n_grid_cells"] > 0 and st["n_bvh_nodes"] == 0
+    assert np.array_equal(a, b)
