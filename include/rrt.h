@@ -145,7 +145,8 @@ typedef enum rrt_integrator {
  * per-sample radiance. */
 typedef enum rrt_shard_mode {
   RRT_SHARD_NONE = 0,
-  RRT_SHARD_TILE = 1,  /* interleaved 32x32-pixel tiles: tile k belongs to rank k % world */
+  RRT_SHARD_TILE = 1,  /* interleaved 32x32-pixel tiles: tile k belongs to rank k % world; tile row sy is numbered from
+                        * column sy on (wrapping), k = sy * tiles_per_row + (sx - sy) mod tiles_per_row: diagonals, not columns */
   RRT_SHARD_SAMPLE = 2 /* samples [rank*n/world, (rank+1)*n/world) of every pixel          */
 } rrt_shard_mode;
 
@@ -170,7 +171,8 @@ typedef struct rrt_stats {
   int32_t sm_count;
   int32_t kernel_features; /* feature set of the render-kernel instance the last call ran: bit 0 moving
                             * spheres, 1 quads, 2 constant media, 3 non-solid textures, 4 Perlin noise,
-                            * 5 box leaves (63 = the general instance), 6 the scene is walked through grids instead of a tree;
+                            * 5 box leaves (63 = the general instance), 6 the scene is walked through grids instead of a tree,
+                            * 7 and the members of a grid move;
                             * a scene runs on the smallest instance covering it.
                             * RRT_KERNEL=full in the environment at rrt_init forces the general instance (debugging). */
   int32_t n_devices;       /* GPUs behind the last call: 1, the size of an rrt_init_multi group, or the communicator's world */

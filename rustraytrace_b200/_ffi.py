@@ -84,7 +84,7 @@ M_LAMBERTIAN, M_METAL, M_DIELECTRIC, M_DIFFUSE_LIGHT, M_ISOTROPIC, M_EMPTY = ran
 T_SOLID, T_CHECKER, T_IMAGE, T_NOISE = range(4)
 INT_BOOK1, INT_BOOK2, INT_BOOK3 = 1, 2, 3
 SHARD_NONE, SHARD_TILE, SHARD_SAMPLE = 0, 1, 2
-SF_MOTION, SF_QUADS, SF_MEDIA, SF_TEXTURES, SF_NOISE, SF_BOXES, SF_ALL, SF_GRID = 1, 2, 4, 8, 16, 32, 63, 64  # rrt_stats.kernel_features bits
+SF_MOTION, SF_QUADS, SF_MEDIA, SF_TEXTURES, SF_NOISE, SF_BOXES, SF_ALL, SF_GRID, SF_GRID_MOVING = 1, 2, 4, 8, 16, 32, 63, 64, 128  # rrt_stats.kernel_features bits
 BOOK_1, BOOK_2, BOOK_3, BOOK_1_GPU = 1, 2, 3, 4
 OK, ERR_INVALID, ERR_CUDA, ERR_UNSUPPORTED, ERR_NO_DEVICE = 0, -1, -2, -3, -4
 O_BITS = {"aspect_ratio": 1 << 0, "image_width": 1 << 1, "samples_per_pixel": 1 << 2, "max_depth": 1 << 3,

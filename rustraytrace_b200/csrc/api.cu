@@ -151,7 +151,8 @@ static void plan_work(const rrt_camera* cam, const rrt_render_params* p, DevWork
   W.tiles_x = W.stiles_x * 4;
   my_pixels = 0;
   for (int k = tr; k < n_super; k += tw) {
-    int sx = k % W.stiles_x, sy = k / W.stiles_x;
+    int sx, sy;
+    rrt::super_tile_xy(k, W.stiles_x, sx, sy);
     my_pixels += (double)std::min(32, Wd - sx * 32) * (double)std::min(32, H - sy * 32);
   }
 }
@@ -527,7 +528,7 @@ int rrt_shard_plan(const rrt_camera* cam, const rrt_render_params* p, int32_t* s
     const bool tile = W.shard_mode == RRT_SHARD_TILE;
     for (int y = 0; y < W.height; ++y)
       for (int x = 0; x < W.width; ++x) {
-        int k = (y / 32) * W.stiles_x + (x / 32);
+        int k = rrt::super_tile_index(x / 32, y / 32, W.stiles_x);
         owner_mask[(size_t)y * W.width + x] = (!tile || k % W.world == W.rank) ? 1 : 0;
       }
   }

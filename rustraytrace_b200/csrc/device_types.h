@@ -38,6 +38,25 @@ namespace rrt {
 //   q4 = (B0.x, B1.x, B0.y, B1.y)  q5 = (B0.z, B1.z, b0_0, b0_1)
 // Pair k holds quads first+2k and first+2k+1 of the leaf's quad run; a missing partner has n = 0.
 enum PrimKind { PRIM_SPHERE = 0, PRIM_QUAD = 1 };
+
+// Numbering of the 32x32-pixel super tiles for tile sharding (RRT_SHARD_TILE): tile k belongs to rank k % world and
+// is that rank's (k / world)-th.  Row sy of the frame is numbered from column sy on (wrapping), so that a rank's
+// tiles run along diagonals: numbered straight across, a frame whose tile row is a multiple of the rank count (3840
+// pixels = 120 tiles, 8 ranks) gave every rank whole columns, and the Cornell box 5 % of imbalance (profiles/README.md r02r).
+#if defined(__CUDACC__)
+#define RRT_HD __host__ __device__
+#else
+#define RRT_HD
+#endif
+RRT_HD inline int super_tile_index(int sx, int sy, int stiles_x) {
+  int c = sx - sy % stiles_x;
+  if (c < 0) c += stiles_x;
+  return sy * stiles_x + c;
+}
+RRT_HD inline void super_tile_xy(int k, int stiles_x, int& sx, int& sy) {
+  sy = k / stiles_x;
+  sx = (k % stiles_x + sy % stiles_x) % stiles_x;
+}
 enum PrimFlags { PF_UV_ROTATED = 1 };
 
 // ---- BVH inner node (float4 n[4]) ------------------------------------------------------------
@@ -89,7 +108,10 @@ enum SceneFeature {
   // the front run, no tree.  An instance is compiled for one or the other, so that neither carries the other's code
   // (the general book-2 instance with both was 75 KB of SASS, and its warps waited for instruction fetches 1.8 times per
   // issue: profiles/README.md r02l).  A grid scene runs on an instance with this bit, any other on one without.
-  SF_GRID = 64
+  SF_GRID = 64,
+  // ... and a grid's members move (DevGrid::dclo / dchi): rays are clipped to the field's bounds at their own time.
+  // A bit of its own because the code costs the book-2 final scene, whose fields stand still, 2.8 % (profiles/README.md r02u).
+  SF_GRID_MOVING = 128
 };
 
 struct DevMaterial {  // 32 B
@@ -156,12 +178,19 @@ struct DevCamera64 {
 
 #define RRT_MAX_GRIDS 2
 struct DevGrid {
-  float lo[3], hi[3];     // bounds
+  float lo[3], hi[3];     // bounds (of the whole shutter interval): the cells are laid over these
+  // What a ray is clipped to before it walks: the bounds at ray time tm, lo(tm) = clo + tm dclo, hi(tm) = chi + tm dchi.
+  // Linear motion makes the items' extremes at tm at most the interpolated extremes of tm = 0 and tm = 1, so this is
+  // conservative; for the bouncing spheres (the_next_week/mod.rs:96-149: centres rise by up to 0.5) the slab a ray has
+  // to cross is 0.4 + 0.5 tm high instead of 0.9.  Static fields: dclo = dchi = 0.
+  float clo[3], chi[3], dclo[3], dchi[3];
   float cell[3], inv[3];  // cell size and its reciprocal per axis
   int res[3];
   int first_cell;         // offset of this grid's cells in DevScene::grid_cells
   int kind;               // 0: cells list spheres (flat primitive indices), 1: boxes (records of DevScene::boxes)
   int n_items;
+  int moving;             // any of dclo / dchi is not zero
+  int pad_;
 };
 
 struct DevScene {

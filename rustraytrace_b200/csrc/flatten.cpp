@@ -622,6 +622,7 @@ bool tex_needs_ok(const rrt_scene_desc* d, int t, int depth) {
 #endif
 struct GridGeom {
   double lo[3], hi[3], cell[3];
+  double lo0[3], hi0[3], lo1[3], hi1[3];   // the members' bounds at shutter time 0 and 1, padded like lo / hi
   int res[3];
   std::vector<std::vector<int>> lists;   // per cell: item indices
   size_t n_refs = 0, crowded = 0;
@@ -684,6 +685,23 @@ bool grid_geometry(const std::vector<BakedPrim>& items, const std::vector<int>& 
     const double pad = 1e-3 * ext[a] / G.res[a] + 1e-6 * std::max(std::fabs(G.lo[a]), std::fabs(G.hi[a]));   // the bounds, outwards
     G.lo[a] -= pad; G.hi[a] += pad;
     G.cell[a] = (G.hi[a] - G.lo[a]) / G.res[a];
+  }
+  for (int a = 0; a < 3; ++a) {   // bounds at the two ends of the shutter (moving spheres: c0 and c0 + dc), inside lo / hi
+    G.lo0[a] = G.lo1[a] = std::numeric_limits<double>::infinity(); G.hi0[a] = G.hi1[a] = -G.lo0[a];
+    for (int i : members) {
+      const BakedPrim& p = items[i];
+      if (p.kind == PRIM_SPHERE) {
+        const double c0 = p.c0[a], c1 = p.c0[a] + p.dc[a];
+        G.lo0[a] = std::min(G.lo0[a], c0 - p.r); G.hi0[a] = std::max(G.hi0[a], c0 + p.r);
+        G.lo1[a] = std::min(G.lo1[a], c1 - p.r); G.hi1[a] = std::max(G.hi1[a], c1 + p.r);
+      } else {
+        G.lo0[a] = std::min(G.lo0[a], p.lo[a]); G.hi0[a] = std::max(G.hi0[a], p.hi[a]);
+        G.lo1[a] = G.lo0[a]; G.hi1[a] = G.hi0[a];
+      }
+    }
+    const double pad = tiled[a] ? 0.0 : 1e-3 * G.cell[a] + 1e-6 * std::max(std::fabs(G.lo[a]), std::fabs(G.hi[a]));
+    G.lo0[a] = std::max(G.lo[a], G.lo0[a] - pad); G.lo1[a] = std::max(G.lo[a], G.lo1[a] - pad);
+    G.hi0[a] = std::min(G.hi[a], G.hi0[a] + pad); G.hi1[a] = std::min(G.hi[a], G.hi1[a] + pad);
   }
   G.lists.assign((size_t)G.res[0] * G.res[1] * G.res[2], std::vector<int>());
   G.n_refs = 0; G.crowded = 0;
@@ -765,6 +783,11 @@ void emit_grids(const std::vector<BakedPrim>& items, const std::vector<int>& ite
     }
     for (int a = 0; a < 3; ++a) {
       D.lo[a] = (float)G.lo[a]; D.hi[a] = (float)G.hi[a];
+      // clip bounds rounded outwards (towards lo / hi, which they never leave)
+      D.clo[a] = std::max(D.lo[a], std::nextafterf((float)G.lo0[a], -INFINITY)); D.chi[a] = std::min(D.hi[a], std::nextafterf((float)G.hi0[a], INFINITY));
+      const float l1 = std::max(D.lo[a], std::nextafterf((float)G.lo1[a], -INFINITY)), h1 = std::min(D.hi[a], std::nextafterf((float)G.hi1[a], INFINITY));
+      D.dclo[a] = l1 - D.clo[a]; D.dchi[a] = h1 - D.chi[a];
+      if (D.dclo[a] != 0.0f || D.dchi[a] != 0.0f) { D.moving = 1; out.features |= SF_GRID_MOVING; }
       D.cell[a] = (float)G.cell[a]; D.inv[a] = (float)(1.0 / G.cell[a]);
       D.res[a] = G.res[a];
     }

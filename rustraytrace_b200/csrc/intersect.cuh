@@ -305,9 +305,22 @@ __device__ __forceinline__ void leaf1_hit32(const float4* __restrict__ prims, co
 template <int FEAT, int KIND>
 __device__ __forceinline__ void grid_hit32(const DevScene& S, const DevGrid& G, const Ray32& r, float idx, float idy, float idz,
                                            float a, float inv_a, float tmin, int skip, bool motion, Hit32& h) {
-  const float x0 = (G.lo[0] - r.o.x) * idx, x1 = (G.hi[0] - r.o.x) * idx;
-  const float y0 = (G.lo[1] - r.o.y) * idy, y1 = (G.hi[1] - r.o.y) * idy;
-  const float z0 = (G.lo[2] - r.o.z) * idz, z1 = (G.hi[2] - r.o.z) * idz;
+  // the field's bounds at the ray's time (device_types.h DevGrid::clo ..): moving spheres sweep a taller slab than they fill
+#ifdef RRT_NO_TIME_CLIP
+  float lx = G.lo[0], ly = G.lo[1], lz = G.lo[2], hx = G.hi[0], hy = G.hi[1], hz = G.hi[2];
+  if (false) {
+#else
+  const bool tc = (FEAT & SF_GRID_MOVING) != 0;   // (instances without the bit clip to the bounds of the whole shutter interval)
+  float lx = tc ? G.clo[0] : G.lo[0], ly = tc ? G.clo[1] : G.lo[1], lz = tc ? G.clo[2] : G.lo[2];
+  float hx = tc ? G.chi[0] : G.hi[0], hy = tc ? G.chi[1] : G.hi[1], hz = tc ? G.chi[2] : G.hi[2];
+  if ((FEAT & SF_GRID_MOVING) && motion && KIND == 0 && G.moving) {
+#endif
+    lx = fmaf(r.tm, G.dclo[0], lx); ly = fmaf(r.tm, G.dclo[1], ly); lz = fmaf(r.tm, G.dclo[2], lz);
+    hx = fmaf(r.tm, G.dchi[0], hx); hy = fmaf(r.tm, G.dchi[1], hy); hz = fmaf(r.tm, G.dchi[2], hz);
+  }
+  const float x0 = (lx - r.o.x) * idx, x1 = (hx - r.o.x) * idx;
+  const float y0 = (ly - r.o.y) * idy, y1 = (hy - r.o.y) * idy;
+  const float z0 = (lz - r.o.z) * idz, z1 = (hz - r.o.z) * idz;
   const float t0 = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
   const float t1 = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), h.t));
   if (!(t0 <= t1)) return;

@@ -28,7 +28,7 @@ __global__ void probe_kernel32(const __grid_constant__ ProbeArgs A) {
   r.d = V3f(C.p00x + fx * C.dux + fy * C.dvx, C.p00y + fx * C.duy + fy * C.dvy, C.p00z + fx * C.duz + fy * C.dvz);
   r.tm = 0.0f;
   Hit32 h; h.t = CUDART_INF_F; h.prim = -1;
-  if (A.S.n_grids > 0) world_hit32<SF_ALL | SF_GRID>(A.S, r, 0.001f, -1, h);
+  if (A.S.n_grids > 0) world_hit32<SF_ALL | SF_GRID | SF_GRID_MOVING>(A.S, r, 0.001f, -1, h);
   else world_hit32<SF_ALL>(A.S, r, 0.001f, -1, h);
   int id = -1;
   if (h.prim >= 0) {
@@ -56,12 +56,12 @@ __global__ void resolve_kernel(const float4* __restrict__ accum, int n, int spp,
   }
 }
 
-// Tile exchange: super tile k = (y / 32) * stiles_x + x / 32 belongs to rank k % world and is that rank's
+// Tile exchange: super tile k (device_types.h super_tile_index) belongs to rank k % world and is that rank's
 // (k / world)-th; one float4 per pixel, coalesced on both sides (a warp reads one tile row).
 __global__ void tile_scatter_kernel(const __grid_constant__ TileScatterArgs A) {
   const int x = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y;
   if (x >= A.width || y >= A.height) return;
-  const int k = (y >> 5) * A.stiles_x + (x >> 5);
+  const int k = super_tile_index(x >> 5, y >> 5, A.stiles_x);
   const int r = k % A.world, j = k / A.world;
   A.frame[(size_t)y * A.width + x] = A.staging[(size_t)A.off[r] + (size_t)j * 1024 + (y & 31) * 32 + (x & 31)];
 }
@@ -129,13 +129,20 @@ const RenderVariant* select_render_variant(int integrator, int features, bool fo
                          : integrator == RRT_INT_BOOK2 ? render_variants_book2(&n) : render_variants_book3(&n);
   // the way the scene is walked (SF_GRID) must match; among those instances the first that covers the scene, or —
   // force_full — the general one, which is the last of its kind in every table
-  const RenderVariant* general = nullptr;
-  for (int i = 0; i < n; ++i) {
-    if ((t[i].features & SF_GRID) != (features & SF_GRID)) continue;
-    if (!force_full && (t[i].features & features) == features) return &t[i];
-    general = &t[i];
+  // (SF_GRID_MOVING likewise; a table without such an instance — book 1 has no ray time — serves the scene with the
+  // plain grid instances, which clip to the bounds of the whole shutter interval)
+  const int WALK = SF_GRID | SF_GRID_MOVING;
+  for (int pass = 0; pass < 2; ++pass) {
+    const RenderVariant* general = nullptr;
+    for (int i = 0; i < n; ++i) {
+      if ((t[i].features & WALK) != (features & WALK)) continue;
+      if (!force_full && (t[i].features & features) == features) return &t[i];
+      general = &t[i];
+    }
+    if (general) return general;
+    features &= ~SF_GRID_MOVING;
   }
-  return general;
+  return &t[n - 1];
 }
 
 static const void* render_entry(const RenderVariant* v, int schedule) {

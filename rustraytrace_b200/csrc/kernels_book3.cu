@@ -10,6 +10,7 @@ const RenderVariant* render_variants_book3(int* n) {
     {SF_QUADS | SF_MEDIA, render_kernel<RRT_INT_BOOK3, SF_QUADS | SF_MEDIA, true>, render_kernel<RRT_INT_BOOK3, SF_QUADS | SF_MEDIA, false>, nullptr},
     {SF_ALL, render_kernel<RRT_INT_BOOK3, SF_ALL, true>, render_kernel<RRT_INT_BOOK3, SF_ALL, false>, nullptr},
     {SF_GRID | SF_ALL, render_kernel<RRT_INT_BOOK3, SF_GRID | SF_ALL, true>, render_kernel<RRT_INT_BOOK3, SF_GRID | SF_ALL, false>, nullptr},   // scenes walked through grids
+    {SF_GRID | SF_GRID_MOVING | SF_ALL, render_kernel<RRT_INT_BOOK3, SF_GRID | SF_GRID_MOVING | SF_ALL, true>, render_kernel<RRT_INT_BOOK3, SF_GRID | SF_GRID_MOVING | SF_ALL, false>, nullptr},
   };
   *n = (int)(sizeof table / sizeof table[0]);
   return table;

@@ -297,7 +297,7 @@ int rrt_tile_scatter_host(const rrt_camera* cam, int world, const float* const* 
   const FramePlan f = plan_frame(cam, world);
   for (int y = 0; y < f.height; ++y)
     for (int x = 0; x < f.width; ++x) {
-      const int k = (y >> 5) * f.stiles_x + (x >> 5);
+      const int k = rrt::super_tile_index(x >> 5, y >> 5, f.stiles_x);
       const int r = k % world, j = k / world;
       if (!shares[r]) return rrt::fail(RRT_ERR_INVALID, "rrt_tile_scatter_host: a share is null");
       std::memcpy(frame + ((size_t)y * f.width + x) * 4, shares[r] + ((size_t)j * 1024 + (y & 31) * 32 + (x & 31)) * 4, 4 * sizeof(float));

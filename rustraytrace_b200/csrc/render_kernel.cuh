@@ -51,13 +51,14 @@ __device__ inline float clampf(float x, float lo, float hi) { return fminf(fmaxf
 __device__ inline bool finite3(V3f v) { return isfinite(v.x + v.y + v.z); }  // radiance is >= 0: the sum is finite iff all three are
 
 // tile index of this rank -> top-left pixel.  Super tiles are 32x32 pixels = 4x8 warp tiles;
-// super tile k belongs to rank k % world (RRT_SHARD_TILE); otherwise world == 1.
+// super tile k (device_types.h super_tile_xy) belongs to rank k % world (RRT_SHARD_TILE); otherwise world == 1.
 __device__ inline void tile_origin(const DevWork& W, int tile, int& px0, int& py0) {
   int sj = tile >> 5, within = tile & 31;
   int world = W.shard_mode == RRT_SHARD_TILE ? W.world : 1;
   int rank = W.shard_mode == RRT_SHARD_TILE ? W.rank : 0;
   int k = rank + sj * world;
-  int sx = k % W.stiles_x, sy = k / W.stiles_x;
+  int sx, sy;
+  super_tile_xy(k, W.stiles_x, sx, sy);
   px0 = sx * 32 + (within & 3) * 8;
   py0 = sy * 32 + (within >> 2) * 4;
 }

@@ -37,14 +37,16 @@ def init_comm_from_torch(ctx, group=None):
 
 def pack_tiles_host(frame, rank, world):
     """Host mirror of the kernel's compact tile layout (tests): the super tiles of `frame` (H, W, 4) that
-    belong to `rank` — tile k = (y // 32) * ceil(W / 32) + x // 32 with k % world == rank — back to back,
+    belong to `rank` — tile k with k % world == rank, where row sy of the frame is numbered from column sy on
+    (device_types.h super_tile_xy: sy = k // sx, column (k % sx + sy) % sx) — back to back,
     1024 RGBA pixels each, row-major inside a tile, zero where a tile hangs over the frame's edge."""
     H, W = frame.shape[:2]
     sx, sy = (W + 31) // 32, (H + 31) // 32
     ks = list(range(rank, sx * sy, world))
     out = np.zeros((len(ks), 32, 32, 4), dtype=np.float32)
     for j, k in enumerate(ks):
-        y0, x0 = (k // sx) * 32, (k % sx) * 32
+        ty = k // sx
+        y0, x0 = ty * 32, ((k % sx + ty) % sx) * 32
         blk = frame[y0:y0 + 32, x0:x0 + 32]
         out[j, :blk.shape[0], :blk.shape[1]] = blk
     return out.reshape(-1)

@@ -90,7 +90,7 @@ def test_scene_feature_bits_select_the_kernel_instance():
         s = R.BookScene(book, no, overrides=dict(image_width=64))
         return R.scene_features(s.desc)
     assert feat("in_one_weekend") == F.SF_GRID              # a field of spheres: walked through a grid, no tree
-    assert feat("the_next_week", 1) == F.SF_GRID | F.SF_MOTION | F.SF_TEXTURES   # bouncing spheres on a checker ground
+    assert feat("the_next_week", 1) == F.SF_GRID | F.SF_GRID_MOVING | F.SF_MOTION | F.SF_TEXTURES   # bouncing spheres on a checker ground
     assert feat("the_next_week", 3) == F.SF_TEXTURES        # earth (image texture)
     assert feat("the_next_week", 4) == F.SF_TEXTURES | F.SF_NOISE   # perlin
     assert feat("the_next_week", 6) == F.SF_QUADS | F.SF_TEXTURES | F.SF_NOISE   # simple light over perlin spheres

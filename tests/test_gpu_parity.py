@@ -170,7 +170,7 @@ def test_teardown_in_either_order_is_safe():
 
 
 @pytest.mark.parametrize("book,scene_no,feat", [
-    ("in_one_weekend", None, F.SF_GRID), ("the_next_week", 1, F.SF_GRID | F.SF_MOTION | F.SF_TEXTURES), ("the_next_week", 3, F.SF_TEXTURES), ("the_next_week", 4, F.SF_TEXTURES | F.SF_NOISE),
+    ("in_one_weekend", None, F.SF_GRID), ("the_next_week", 1, F.SF_GRID | F.SF_GRID_MOVING | F.SF_MOTION | F.SF_TEXTURES), ("the_next_week", 3, F.SF_TEXTURES), ("the_next_week", 4, F.SF_TEXTURES | F.SF_NOISE),
     ("the_next_week", 5, F.SF_QUADS), ("the_next_week", 6, F.SF_QUADS | F.SF_TEXTURES | F.SF_NOISE),
     ("the_next_week", 8, F.SF_QUADS | F.SF_MEDIA), ("the_next_week", 9, F.SF_ALL | F.SF_GRID), ("the_rest_of_your_life", None, F.SF_QUADS)])
 def test_specialised_kernel_instance_equals_the_general_one(ctx, book, scene_no, feat, monkeypatch):
@@ -186,7 +186,7 @@ def test_specialised_kernel_instance_equals_the_general_one(ctx, book, scene_no,
     monkeypatch.delenv("RRT_KERNEL")
     gf = full.scene(s.desc)
     b = full.render(gf, s.camera, s.integrator, seed=5).astype(np.float64)
-    assert full.stats()["kernel_features"] == F.SF_ALL | (feat & F.SF_GRID)
+    assert full.stats()["kernel_features"] == F.SF_ALL | (feat & (F.SF_GRID | F.SF_GRID_MOVING))
     gf.close(); full.close(); gs.close()
     assert np.array_equal(a[..., 3], b[..., 3])
     ma, mb = a[..., :3].mean(axis=(0, 1)), b[..., :3].mean(axis=(0, 1))

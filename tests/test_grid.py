@@ -189,3 +189,65 @@ def test_one_shot_render_without_a_tree_is_the_same_frame(book, scene_no, monkey
     ctx.close()
     assert st["n_grid_cells"] > 0 and st["n_bvh_nodes"] == 0
     assert np.array_equal(a, b)
+
+
+def random_boxes(seed, n_boxes, n_spheres, lattice):
+    """Axis-aligned boxes (make_box: six quads as a list) — on a lattice of equal footprints or scattered with random
+    sizes — plus a cloud of equal spheres and a few odd primitives for the front run."""
+    rng = np.random.default_rng(1000 + seed)
+    b = R.DescBuilder()
+    mats = [b.lambertian(tuple(rng.uniform(0.2, 0.9, 3))) for _ in range(3)] + [b.material(F.M_DIELECTRIC, ri=1.5)]
+
+    def box(lo, hi, mat):
+        (x0, y0, z0), (x1, y1, z1) = lo, hi
+        dx, dy, dz = (x1 - x0, 0, 0), (0, y1 - y0, 0), (0, 0, z1 - z0)
+        neg = lambda v: tuple(-c for c in v)
+        return b.list([b.quad((x0, y0, z1), dx, dy, mat), b.quad((x1, y0, z1), neg(dz), dy, mat), b.quad((x1, y0, z0), neg(dx), dy, mat),
+                       b.quad((x0, y0, z0), dz, dy, mat), b.quad((x0, y1, z1), dx, neg(dz), mat), b.quad((x0, y0, z0), dx, dz, mat)])
+    items = []
+    side = int(np.ceil(np.sqrt(n_boxes)))
+    for k in range(n_boxes):
+        m = mats[rng.integers(3)]
+        if lattice:
+            i, j = k % side, k // side
+            lo = (-4.0 + i * 1.0, -1.0, -4.0 + j * 1.0)
+            hi = (lo[0] + 1.0, -1.0 + float(rng.uniform(0.1, 1.0)), lo[2] + 1.0)
+        else:
+            lo = tuple(rng.uniform(-4, 3.5, 3) * np.array([1.0, 0.3, 1.0]))
+            hi = tuple(np.array(lo) + rng.uniform(0.3, 0.6, 3))
+        items.append(box(lo, hi, m))
+    for _ in range(n_spheres):
+        items.append(b.sphere(tuple(rng.uniform(-3, 3, 3) * np.array([1.0, 0.5, 1.0]) + np.array([0, 2.0, 0])), 0.25, mats[rng.integers(4)]))
+    items.append(b.sphere((0.0, -1001.0, 0.0), 1000.0, mats[0]))
+    items.append(b.quad((-2.0, 4.0, -2.0), (4.0, 0.0, 0.0), (0.0, 0.0, 4.0), mats[1]))
+    cam = R.make_camera(image_width=144, aspect_ratio=1.0, samples_per_pixel=16, max_depth=8, background=(0.6, 0.7, 0.9),
+                        vfov=45.0, lookfrom=(float(rng.uniform(-3, 3)), float(rng.uniform(2.0, 5.0)), 12.0), lookat=(0.0, 0.0, 0.0))
+    return b.desc(b.list(items)), cam
+
+
+@pytest.mark.parametrize("seed,lattice", [(0, True), (1, True), (2, False), (3, False)])
+def test_box_fields_pass_the_flattener_check(seed, lattice, monkeypatch):
+    d, _ = random_boxes(seed, 64 + 17 * seed, 80, lattice)
+    monkeypatch.setenv("RRT_FORCE_GRID", "1")
+    boxes, spheres = R.flatten_grid(d, 1), R.flatten_grid(d, 0)
+    assert boxes["n_items"] == 64 + 17 * seed and spheres["n_items"] >= 80
+    if lattice and seed == 0:
+        assert boxes["max_per_cell"] == 1 and boxes["res"][0] == 8 and boxes["res"][2] == 8    # 64 boxes tile 8 x 8
+    R.flatten_check(d)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed,lattice", [(0, True), (1, True), (2, False), (3, False)])
+def test_box_and_sphere_grids_match_the_tree(seed, lattice, monkeypatch):
+    """Scattered boxes go through the padded membership (every cell their bounds touch), lattice boxes through the
+    one-box-per-cell tiles; either way the walk must find the tree's hits (lattice: up to roundings at box edges)."""
+    d, cam = random_boxes(seed, 64 + 17 * seed, 80, lattice)
+    (ids, t, a), (pids, pt, b) = _both(d, cam, F.INT_BOOK2, monkeypatch, force=True)
+    assert (ids >= 0).any()
+    if lattice:
+        assert (ids != pids).mean() <= 2e-4
+        assert np.array_equal(a[..., 3], b[..., 3])
+        assert (np.abs(a[..., :3] - b[..., :3]).max(axis=2) > 1e-6 * np.maximum(b[..., :3].max(axis=2), 1e-3)).mean() <= 2e-3
+    else:
+        assert np.array_equal(ids, pids) and np.array_equal(t, pt)
+        assert np.array_equal(a, b)
