@@ -27,6 +27,7 @@ static void usage() {
   std::fprintf(stderr, "render flags (RenderOverrides, src/config.rs:1-14): --width N --spp N --depth N --aspect R --vfov D\n"
                        "  --lookfrom x,y,z --lookat x,y,z --vup x,y,z --defocus-angle D --focus-dist F --background r,g,b\n"
                        "  --no-overrides (scene defaults)  --seed N (scene RNG)  --sample-seed N  --device N  -o FILE  --probe\n"
+                       "  --p6             binary PPM (P6; gamma and quantisation on the GPU, rrt_resolve_rgb8) instead of the text P3\n"
                        "  --devices 0,1,..  render on several GPUs of this box (sample ranges + NCCL reduce; --shard tile: interleaved\n"
                        "                    32x32 tiles + gather)\n");
 }
@@ -41,7 +42,7 @@ int main(int argc, char** argv) {
   std::vector<int> devices;   // --devices: a multi-GPU group (rrt_init_multi)
   int shard_mode = RRT_SHARD_NONE;
   const char* out_path = nullptr;
-  bool probe = false;
+  bool probe = false, p6 = false;
   for (int i = 1; i < argc; ++i) {
     std::string a = argv[i];
     auto next = [&](const char* what) -> const char* {
@@ -87,6 +88,7 @@ int main(int argc, char** argv) {
     }
     if (a == "-o") { out_path = next("-o"); continue; }
     if (a == "--probe") { probe = true; continue; }
+    if (a == "--p6") { p6 = true; continue; }
     if (a == "-h" || a == "--help") { usage(); return 0; }
     positional.push_back(a);
   }
@@ -164,8 +166,24 @@ int main(int argc, char** argv) {
       rrt_get_stats(ctx, &st);
       std::fprintf(stderr, "Done: %.0f paths in %.1f ms (%.1f Mpaths/s), %d prims, %d BVH nodes, %d GPU(s), exchange %.2f ms\n", st.paths,
                    st.kernel_ms, st.paths / st.kernel_ms / 1e3, st.n_prims, st.n_bvh_nodes, st.n_devices, st.exchange_ms);
+      std::vector<uint8_t> rgb;
+      if (p6) {   // write_color's arithmetic (color.rs:19-36) on the device, three bytes a pixel
+        rgb.resize((size_t)W * H * 3);
+        if (rrt_resolve_rgb8(ctx, accum.data(), W, H, st.spp_effective, rgb.data()) != RRT_OK) {
+          std::fprintf(stderr, "CUDA resolve failed: %s\n", rrt_last_error());
+          rc = 1;
+        }
+      }
       restore_stdout();
-      if (rrth_write_ppm_from_accum(out_path, W, H, accum.data(), (uint32_t)st.spp_effective) != 0) {
+      if (p6) {
+        FILE* f = rc ? nullptr : (out_path ? std::fopen(out_path, "wb") : stdout);
+        if (!f) { if (!rc) std::perror(out_path); rc = 1; }
+        else {
+          std::fprintf(f, "P6\n%d %d\n255\n", W, H);
+          if (std::fwrite(rgb.data(), 1, rgb.size(), f) != rgb.size()) rc = 1;
+          if (out_path) std::fclose(f); else std::fflush(f);
+        }
+      } else if (rrth_write_ppm_from_accum(out_path, W, H, accum.data(), (uint32_t)st.spp_effective) != 0) {
         std::fprintf(stderr, "could not write the image: %s\n", rrth_last_error());
         rc = 1;
       }

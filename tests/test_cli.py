@@ -67,3 +67,22 @@ def test_cli_devices_flag_renders_on_a_group(devices, shard):
     assert a.shape == b.shape and np.abs(a - b).max() <= 1 and (a != b).mean() < 0.01
     bad = subprocess.run([RRT, "weekend", "--devices", "0,0"], capture_output=True, text=True, timeout=60)
     assert bad.returncode == 1 and "listed twice" in bad.stderr
+
+
+def test_cli_binary_ppm_holds_the_same_pixels_as_the_text_ppm(tmp_path):
+    """--p6: the resolve runs on the GPU (rrt_resolve_rgb8) and the file is a binary PPM; same bytes as the P3 numbers
+    (write_color, color.rs:19-36), up to the last-bit freedom of the atomically summed sample chunks."""
+    args = ["the_next_week", "2", "--width", "80", "--spp", "32", "--depth", "8", "--sample-seed", "3"]
+    text = subprocess.run([RRT] + args, capture_output=True, text=True, timeout=120)
+    assert text.returncode == 0, text.stderr
+    out = str(tmp_path / "img.ppm")
+    binary = subprocess.run([RRT] + args + ["--p6", "-o", out], capture_output=True, timeout=120)
+    assert binary.returncode == 0, binary.stderr
+    raw = open(out, "rb").read()
+    head = raw.split(b"\n", 3)
+    assert head[0] == b"P6" and head[2] == b"255"
+    w, h = (int(x) for x in head[1].split())
+    img = np.frombuffer(head[3], dtype=np.uint8).reshape(h, w, 3).astype(np.int64)
+    want = read_p3(text.stdout)
+    assert img.shape == want.shape == (45, 80, 3)
+    assert np.abs(img - want).max() <= 1 and (img != want).mean() < 0.01
