@@ -187,6 +187,7 @@ int rrt::render_enqueue(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, 
     long long want = ((steal ? 96 : 48) * resident_warps + W.n_tiles - 1) / W.n_tiles;
     long long cap = std::max(1, n_samples / (steal ? 8 : 16));
     chunks = std::max(1LL, std::min(want, cap));
+    if (const char* e = std::getenv("RRT_CHUNKS")) chunks = std::max(1L, std::min((long)n_samples, std::atol(e)));   // A/B of the work-item size
     if (c->deterministic) chunks = 1;   // one float4 store per pixel, samples summed in index order by one lane
   }
   W.chunks = (int)chunks;
