@@ -185,7 +185,9 @@ int rrt::render_enqueue(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, 
     // work items per resident warp / fewest samples per lane and item (measured: profiles/README.md):
     // with stealing a short item has no intra-warp tail, so items can be smaller
     long long want = ((steal ? 96 : 48) * resident_warps + W.n_tiles - 1) / W.n_tiles;
-    long long cap = std::max(1, n_samples / (steal ? 8 : 16));
+    // at least 16 samples per lane and item: with 8 (tried for the stealing instances) a share of 62 spp — what one of
+    // 8 GPUs gets of C2 — ran 2.3 % slower, 125 spp 4 % (profiles/README.md r02x)
+    long long cap = std::max(1, n_samples / 16);
     chunks = std::max(1LL, std::min(want, cap));
     if (const char* e = std::getenv("RRT_CHUNKS")) chunks = std::max(1L, std::min((long)n_samples, std::atol(e)));   // A/B of the work-item size
     if (c->deterministic) chunks = 1;   // one float4 store per pixel, samples summed in index order by one lane
