@@ -793,20 +793,19 @@ extern "C" int rrt_flatten_check(const rrt_scene_desc* desc, int32_t* n_prims, i
           c1[a] = std::max(0, std::min(G.res[a] - 1, (int)((hi[a] - G.lo[a]) * G.inv[a])));
         }
         for (int z = c0[2]; z <= c1[2]; ++z) for (int y = c0[1]; y <= c1[1]; ++y) for (int x = c0[0]; x <= c1[0]; ++x) {
-          if (G.kind == 0) {   // a sphere at rest has to be listed only where the sphere itself reaches (here: 99.99 % of its radius)
+          if (G.kind == 0) {   // a sphere has to be listed only where the sphere itself reaches (here: 99.99 % of its radius)
             const float4 p0 = F.prims[4 * p], p1 = F.prims[4 * p + 1];
-            if (p1.x == 0.0f && p1.y == 0.0f && p1.z == 0.0f) {
-              const float c[3] = {p0.x, p0.y, p0.z};
-              const int ci[3] = {x, y, z};
-              double d2 = 0;
-              for (int a = 0; a < 3; ++a) {
-                const double lo2 = G.lo[a] + ci[a] * (double)G.cell[a], hi2 = lo2 + G.cell[a];
-                const double d = c[a] < lo2 ? lo2 - c[a] : (c[a] > hi2 ? c[a] - hi2 : 0.0);
-                d2 += d * d;
-              }
-              const double rr = 0.9999 * std::fabs(p0.w);
-              if (d2 > rr * rr) continue;
+            const float c[3] = {p0.x, p0.y, p0.z}, dc[3] = {p1.x, p1.y, p1.z};
+            const int ci[3] = {x, y, z};
+            double d2 = 0;
+            for (int a = 0; a < 3; ++a) {   // from the box of the centre's path, per axis
+              const double lo2 = G.lo[a] + ci[a] * (double)G.cell[a], hi2 = lo2 + G.cell[a];
+              const double ca = std::min(c[a], c[a] + dc[a]), cb = std::max(c[a], c[a] + dc[a]);
+              const double d = cb < lo2 ? lo2 - cb : (ca > hi2 ? ca - hi2 : 0.0);
+              d2 += d * d;
             }
+            const double rr = 0.9999 * std::fabs(p0.w);
+            if (d2 > rr * rr) continue;
           }
           const unsigned h = F.grid_cells[G.first_cell + ((size_t)z * G.res[1] + y) * G.res[0] + x];
           bool found = false;

@@ -714,10 +714,11 @@ bool grid_geometry(const std::vector<BakedPrim>& items, const std::vector<int>& 
       c0[a] = std::max(0, std::min(G.res[a] - 1, (int)std::floor((items[i].lo[a] - pad - G.lo[a]) / G.cell[a])));
       c1[a] = std::max(0, std::min(G.res[a] - 1, (int)std::floor((items[i].hi[a] + pad - G.lo[a]) / G.cell[a])));
     }
-    // a sphere at rest is listed where the SPHERE reaches, not where its box does: the cells at the corners of the box
-    // go (a quarter of the references of the book-2 cloud, whose spheres are wider than its cells)
+    // a sphere is listed where the SPHERE reaches, not where its box does: the cells at the corners of the box go
+    // (a sixth of the references of the book-2 cloud, whose spheres are wider than its cells).  A moving sphere is
+    // measured from the box of its centre's path, per axis — exact for motion along an axis, conservative otherwise.
     const BakedPrim& it = items[i];
-    const bool ball = it.kind == PRIM_SPHERE && it.dc.x == 0.0 && it.dc.y == 0.0 && it.dc.z == 0.0 && !std::getenv("RRT_GRID_BOX_MEMBERSHIP");
+    const bool ball = it.kind == PRIM_SPHERE && !std::getenv("RRT_GRID_BOX_MEMBERSHIP");
     for (int z = c0[2]; z <= c1[2]; ++z)
       for (int y = c0[1]; y <= c1[1]; ++y)
         for (int x = c0[0]; x <= c1[0]; ++x) {
@@ -727,7 +728,8 @@ bool grid_geometry(const std::vector<BakedPrim>& items, const std::vector<int>& 
             for (int a = 0; a < 3; ++a) {
               const double pad = 1e-3 * G.cell[a] + 4e-6 * std::fabs(it.c0[a]);
               const double lo = G.lo[a] + c[a] * G.cell[a] - pad, hi = G.lo[a] + (c[a] + 1) * G.cell[a] + pad;
-              const double d = it.c0[a] < lo ? lo - it.c0[a] : (it.c0[a] > hi ? it.c0[a] - hi : 0.0);
+              const double ca = std::min(it.c0[a], it.c0[a] + it.dc[a]), cb = std::max(it.c0[a], it.c0[a] + it.dc[a]);
+              const double d = cb < lo ? lo - cb : (ca > hi ? ca - hi : 0.0);
               d2 += d * d;
             }
             if (d2 > it.r * it.r) continue;
