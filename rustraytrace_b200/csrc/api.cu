@@ -189,6 +189,9 @@ int rrt::render_enqueue(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, 
     // 8 GPUs gets of C2 — ran 2.3 % slower, 125 spp 4 % (profiles/README.md r02x)
     long long cap = std::max(1, n_samples / 16);
     chunks = std::max(1LL, std::min(want, cap));
+    // ... unless that leaves fewer than six items a resident warp (a small frame: C1 has 2 850 tiles for 4 736 warps and
+    // lost 4 % to the end of the launch with 6 chunks of its 100 spp instead of 12): then 8 samples
+    if (steal && W.n_tiles * chunks < 6 * resident_warps) chunks = std::max(1LL, std::min(want, (long long)std::max(1, n_samples / 8)));
     if (const char* e = std::getenv("RRT_CHUNKS")) chunks = std::max(1L, std::min((long)n_samples, std::atol(e)));   // A/B of the work-item size
     if (c->deterministic) chunks = 1;   // one float4 store per pixel, samples summed in index order by one lane
   }
