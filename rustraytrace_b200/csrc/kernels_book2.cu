@@ -18,7 +18,7 @@ const RenderVariant* render_variants_book2(int* n) {
     // scenes walked through grids (device_types.h SF_GRID): static spheres, the bouncing spheres, and the general instance (the final scene)
     {SF_GRID, render_kernel<RRT_INT_BOOK2, SF_GRID, true>, render_kernel<RRT_INT_BOOK2, SF_GRID, false>, nullptr},
     {SF_GRID | SF_GRID_MOVING | SF_MOTION | SF_TEXTURES, render_kernel<RRT_INT_BOOK2, SF_GRID | SF_GRID_MOVING | SF_MOTION | SF_TEXTURES, true>, render_kernel<RRT_INT_BOOK2, SF_GRID | SF_GRID_MOVING | SF_MOTION | SF_TEXTURES, false>, nullptr},
-    {SF_GRID | SF_ALL, render_kernel<RRT_INT_BOOK2, SF_GRID | SF_ALL, true>, render_kernel<RRT_INT_BOOK2, SF_GRID | SF_ALL, false>, nullptr},
+    {SF_GRID | SF_ALL, render_kernel<RRT_INT_BOOK2, SF_GRID | SF_ALL, true>, render_kernel<RRT_INT_BOOK2, SF_GRID | SF_ALL, false>, render_kernel_pool<RRT_INT_BOOK2, SF_GRID | SF_ALL>},
     {SF_GRID | SF_GRID_MOVING | SF_ALL, render_kernel<RRT_INT_BOOK2, SF_GRID | SF_GRID_MOVING | SF_ALL, true>, render_kernel<RRT_INT_BOOK2, SF_GRID | SF_GRID_MOVING | SF_ALL, false>, nullptr},
   };
   *n = (int)(sizeof table / sizeof table[0]);
