@@ -1026,7 +1026,8 @@ int flatten_scene(const rrt_scene_desc* desc, FlatScene& out, std::string& err, 
   std::vector<BakedPrim> front(items.begin(), items.begin() + n_front);
   items.erase(items.begin(), items.begin() + n_front);
   Builder B(items, single ? (int)items.size() : max_leaf);
-  B.pair_leaves = std::getenv("RRT_PAIR_LEAVES") != nullptr;
+  // (scripts/warp_sim.cpp only, with SIM_MAX_LEAF=2: the render kernel tests one primitive per leaf, so never at max_leaf 1)
+  B.pair_leaves = max_leaf >= 2 && std::getenv("RRT_PAIR_LEAVES") != nullptr;
   int root = 0;
   if (single) {
     B.nodes.push_back(BNode());
