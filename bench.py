@@ -255,11 +255,10 @@ def measure(ctx, key, mode, rank, world, steps, warmup, stream, flush, e2e_steps
                 s2 = ctx.stats()
                 h2d, d2h = s2["h2d_bytes"], s2["d2h_bytes"]
             else:
-                g2 = ctx.scene(scene.desc)          # flatten + BVH build + H2D on every rank
-                h2d = ctx.stats()["h2d_bytes"]
-                ctx.render_collective(g2, scene.camera, scene.integrator, seed=1, shard_mode=shard, out=host_np)
-                d2h = ctx.stats()["d2h_bytes"]
-                g2.close()
+                # flatten + H2D on every rank, share, exchange, D2H on rank 0, free: the collective twin of rrt_render_frame
+                ctx.render_frame_collective(scene.desc, scene.camera, scene.integrator, seed=1, shard_mode=shard, out=host_np)
+                s2 = ctx.stats()
+                h2d, d2h = s2["h2d_bytes"], s2["d2h_bytes"]
             barrier()
             if i > 0:
                 e2e_s += time.perf_counter() - t0
@@ -269,7 +268,7 @@ def measure(ctx, key, mode, rank, world, steps, warmup, stream, flush, e2e_steps
         out["e2e"] = {"value": round(total_paths / steps * e2e_steps / t.item() / 1e6, 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                       "d2h_bytes_per_step": int(d2h), "steps": e2e_steps, "ms_per_step": round(1e3 * t.item() / e2e_steps, 3),
                       "call": "rrt_render_frame (host scene description in, pinned RGBA-sum frame out)" if world == 1 else
-                              "rrt_scene_create + rrt_render_collective (share + NCCL exchange in librrt.so, pinned frame out on rank 0), every rank"}
+                              "rrt_render_frame_collective (host scene description in on every rank, share + NCCL exchange in librrt.so, pinned frame out on rank 0)"}
     gs.close()
     return out
 

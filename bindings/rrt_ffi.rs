@@ -43,6 +43,7 @@ extern "C" {
     pub fn rrt_comm_init(ctx: *mut RrtCtx, id128: *const u8, rank: c_int, world: c_int) -> c_int;
     pub fn rrt_render_collective(ctx: *mut RrtCtx, scene: *const RrtScene, cam: *const RrtCamera, p: *const RrtRenderParams,
                                  accum_dev_root: *mut f32, accum_host_root: *mut f32) -> c_int;
+    pub fn rrt_render_frame_collective(ctx: *mut RrtCtx, desc: *const RrtSceneDesc, cam: *const RrtCamera, p: *const RrtRenderParams, accum_host_root: *mut f32) -> c_int;
     pub fn rrt_tile_scatter_host(cam: *const RrtCamera, world: c_int, shares: *const *const f32, frame: *mut f32) -> c_int;
     pub fn rrt_set_stream(ctx: *mut RrtCtx, cuda_stream: *mut c_void) -> c_int;
     pub fn rrt_scene_create(ctx: *mut RrtCtx, desc: *const RrtSceneDesc, out: *mut *mut RrtScene) -> c_int;

@@ -227,6 +227,10 @@ int rrt_comm_unique_id(uint8_t* id128);
 int rrt_comm_init(rrt_ctx* ctx, const uint8_t* id128, int rank, int world);
 int rrt_render_collective(rrt_ctx* ctx, const rrt_scene* scene, const rrt_camera* cam,
                           const rrt_render_params* params, float* accum_dev_root, float* accum_host_root);
+/* rrt_render_frame for (B): every rank passes the same description; upload, this rank's share, exchange, free — one
+ * call, as the reference's one blocking render (src/cuda/mod.rs:342).  The frame arrives in accum_host_root on rank 0. */
+int rrt_render_frame_collective(rrt_ctx* ctx, const rrt_scene_desc* desc, const rrt_camera* cam,
+                                const rrt_render_params* params, float* accum_host_root);
 /* Host-only mirror of the tile exchange's last step (tests): shares[r] = rank r's compact tiles
  * (owned 32x32 super tiles back to back, 1024 RGBA pixels each, row-major inside a tile; super tile k
  * belongs to rank k % world and is its (k / world)-th) -> row-major RGBA frame. */

@@ -101,6 +101,7 @@ RRT_SYMBOLS = [
     ("rrt_comm_unique_id", c_int, [VP]),
     ("rrt_comm_init", c_int, [VP, VP, c_int, c_int]),
     ("rrt_render_collective", c_int, [VP, VP, C.POINTER(Camera), C.POINTER(RenderParams), VP, VP]),
+    ("rrt_render_frame_collective", c_int, [VP, C.POINTER(SceneDesc), C.POINTER(Camera), C.POINTER(RenderParams), VP]),
     ("rrt_tile_scatter_host", c_int, [C.POINTER(Camera), c_int, C.POINTER(VP), VP]),
     ("rrt_set_stream", c_int, [VP, VP]),
     ("rrt_scene_create", c_int, [VP, C.POINTER(SceneDesc), C.POINTER(VP)]),

@@ -303,6 +303,13 @@ class Context:
                                              out.ctypes.data if out is not None else None))
         return out
 
+    def render_frame_collective(self, desc, camera, integrator, seed=1, shard_mode=F.SHARD_SAMPLE, out=None):
+        """rrt_render_frame_collective (collective): upload, this rank's share, NCCL exchange, free; the frame lands in `out` on rank 0."""
+        p = self.params(integrator, seed, shard_mode, 0, 1)
+        _check(F.rrt().rrt_render_frame_collective(self._h, C.byref(desc), C.byref(camera), C.byref(p),
+                                                   out.ctypes.data if out is not None else None))
+        return out
+
     def close(self):
         if self._h:
             F.rrt().rrt_shutdown(self._h)

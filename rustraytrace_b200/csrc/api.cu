@@ -245,6 +245,29 @@ int rrt::ensure_floats(float** buf, size_t* have, size_t floats, const char* wha
   return RRT_OK;
 }
 
+int rrt::scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out, bool tree_optional) {
+  if (!c || !out) return fail(RRT_ERR_INVALID, "rrt_scene_create: null argument");
+  *out = nullptr;
+  FlatScene F;
+  std::string err;
+  int st = flatten_scene(desc, F, err, RRT_SINGLE_LEAF_MAX, 1, tree_optional);
+  if (st != RRT_OK) return fail(st, "scene flatten failed: " + err);
+  if (F.bvh_depth >= RRT_STACK)   // the traversal stack holds one entry per level (intersect.cuh)
+    return fail(RRT_ERR_UNSUPPORTED, "BVH depth " + std::to_string(F.bvh_depth) + " exceeds the traversal stack (" + std::to_string(RRT_STACK) + ")");
+  if (F.media.size() > 5) return fail(RRT_ERR_UNSUPPORTED, "more than 5 constant media");
+  rrt_scene* sc = nullptr;
+  int rc = c->members.empty() ? rrt::scene_upload(c, F, &sc) : rrt::multi_scene_create(c, F, &sc);
+  if (rc) return rc;
+  const rrt_scene* p0 = part0_of(sc);
+  c->stats.h2d_bytes = sc->h2d_bytes;
+  c->stats.n_prims = p0->n_prims; c->stats.n_bvh_nodes = p0->n_nodes;
+  c->stats.n_media = p0->n_media; c->stats.n_lights = p0->n_lights;
+  c->stats.n_grid_cells = p0->n_grid_cells;
+  *out = sc;
+  return RRT_OK;
+}
+
+
 extern "C" {
 
 const char* rrt_last_error(void) { return g_err.c_str(); }
@@ -380,29 +403,7 @@ void rrt_scene_destroy(rrt_scene* sc) {
   delete sc;
 }
 
-static int scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out, bool tree_optional) {
-  if (!c || !out) return fail(RRT_ERR_INVALID, "rrt_scene_create: null argument");
-  *out = nullptr;
-  FlatScene F;
-  std::string err;
-  int st = flatten_scene(desc, F, err, RRT_SINGLE_LEAF_MAX, 1, tree_optional);
-  if (st != RRT_OK) return fail(st, "scene flatten failed: " + err);
-  if (F.bvh_depth >= RRT_STACK)   // the traversal stack holds one entry per level (intersect.cuh)
-    return fail(RRT_ERR_UNSUPPORTED, "BVH depth " + std::to_string(F.bvh_depth) + " exceeds the traversal stack (" + std::to_string(RRT_STACK) + ")");
-  if (F.media.size() > 5) return fail(RRT_ERR_UNSUPPORTED, "more than 5 constant media");
-  rrt_scene* sc = nullptr;
-  int rc = c->members.empty() ? rrt::scene_upload(c, F, &sc) : rrt::multi_scene_create(c, F, &sc);
-  if (rc) return rc;
-  const rrt_scene* p0 = part0_of(sc);
-  c->stats.h2d_bytes = sc->h2d_bytes;
-  c->stats.n_prims = p0->n_prims; c->stats.n_bvh_nodes = p0->n_nodes;
-  c->stats.n_media = p0->n_media; c->stats.n_lights = p0->n_lights;
-  c->stats.n_grid_cells = p0->n_grid_cells;
-  *out = sc;
-  return RRT_OK;
-}
-
-int rrt_scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out) { return scene_create(c, desc, out, false); }
+int rrt_scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out) { return rrt::scene_create(c, desc, out, false); }
 
 int rrt_image_height(const rrt_camera* cam) {
   if (!cam || !(cam->aspect_ratio > 0.0)) return 0;
@@ -448,7 +449,7 @@ int rrt_render(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, const rrt
 int rrt_render_frame(rrt_ctx* c, const rrt_scene_desc* desc, const rrt_camera* cam, const rrt_render_params* p,
                      float* accum_host) {
   rrt_scene* sc = nullptr;
-  int rc = scene_create(c, desc, &sc, true);   // rendered once and freed: no tree where grids do the walking
+  int rc = rrt::scene_create(c, desc, &sc, true);   // rendered once and freed: no tree where grids do the walking
   if (rc) return rc;
   rc = rrt_render(c, sc, cam, p, accum_host);
   uint64_t h2d = sc->h2d_bytes;

@@ -72,6 +72,8 @@ struct ShareInfo {
 
 int check_camera(const rrt_camera* cam, const rrt_render_params* p);
 int scene_upload(rrt_ctx* c, const FlatScene& F, rrt_scene** out);
+// rrt_scene_create; tree_optional: the scene will only be rendered (no BVH where grids do the walking)
+int scene_create(rrt_ctx* c, const rrt_scene_desc* desc, rrt_scene** out, bool tree_optional);
 void scene_release(rrt_scene* sc);  // frees device memory, orphans the handle (does not delete it)
 // Enqueue this rank's share on c->stream: events ev[0] (start), ev[1]/ev[2] around the kernel; no host sync.
 // compact: tile sharding writes the rank's super tiles back to back (1024 float4 each) instead of a

@@ -240,6 +240,18 @@ int rrt_comm_init(rrt_ctx* c, const uint8_t* id128, int rank, int world) {
   return RRT_OK;
 }
 
+int rrt_render_frame_collective(rrt_ctx* c, const rrt_scene_desc* desc, const rrt_camera* cam, const rrt_render_params* p,
+                                float* accum_host_root) {
+  rrt_scene* sc = nullptr;
+  int rc = rrt::scene_create(c, desc, &sc, true);   // rendered once and freed: no tree where grids do the walking
+  if (rc) return rc;
+  rc = rrt_render_collective(c, sc, cam, p, nullptr, accum_host_root);
+  const uint64_t h2d = sc->h2d_bytes;
+  rrt_scene_destroy(sc);
+  if (rc == RRT_OK) c->stats.h2d_bytes = h2d;
+  return rc;
+}
+
 int rrt_render_collective(rrt_ctx* c, const rrt_scene* sc, const rrt_camera* cam, const rrt_render_params* p,
                           float* accum_dev_root, float* accum_host_root) {
   if (!c || !sc || !p) return rrt::fail(RRT_ERR_INVALID, "rrt_render_collective: null argument");

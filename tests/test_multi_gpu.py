@@ -70,7 +70,7 @@ def test_group_context_rejects_bad_device_lists():
     g.close()
 
 
-def _rank(rank, world, conn, mode, seed, q):
+def _rank(rank, world, conn, mode, seed, q, one_shot=False):
     import numpy as np
     import rustraytrace_b200 as R
     s = scene()
@@ -82,25 +82,30 @@ def _rank(rank, world, conn, mode, seed, q):
     else:
         uid = conn.recv()
     c.comm_init(uid, rank, world)
-    gs = c.scene(s.desc)
     out = np.zeros((s.height, s.width, 4), dtype=np.float32) if rank == 0 else None
-    c.render_collective(gs, s.camera, s.integrator, seed=seed, shard_mode=mode, out=out)
-    st = c.stats()
+    if one_shot:   # rrt_render_frame_collective: upload, share, exchange, free in one call
+        c.render_frame_collective(s.desc, s.camera, s.integrator, seed=seed, shard_mode=mode, out=out)
+        st = c.stats()
+    else:
+        gs = c.scene(s.desc)
+        c.render_collective(gs, s.camera, s.integrator, seed=seed, shard_mode=mode, out=out)
+        st = c.stats()
+        gs.close()
     if rank == 0:
         q.put((out, st["n_devices"], st["exchange_ms"]))
-    gs.close(); c.close()
+    c.close()
 
 
 @pytest.mark.parametrize("world", [1, 2])
-@pytest.mark.parametrize("mode", [F.SHARD_SAMPLE, F.SHARD_TILE])
-def test_one_process_per_gpu_collective_render(world, mode):
+@pytest.mark.parametrize("mode,one_shot", [(F.SHARD_SAMPLE, False), (F.SHARD_TILE, False), (F.SHARD_SAMPLE, True), (F.SHARD_TILE, True)])
+def test_one_process_per_gpu_collective_render(world, mode, one_shot):
     if world > n_gpus():
         pytest.skip(f"needs {world} GPUs")
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     pipes = [ctx.Pipe() for _ in range(world - 1)]
-    procs = [ctx.Process(target=_rank, args=(0, world, [p[0] for p in pipes], mode, 9, q))]
-    procs += [ctx.Process(target=_rank, args=(r, world, pipes[r - 1][1], mode, 9, q)) for r in range(1, world)]
+    procs = [ctx.Process(target=_rank, args=(0, world, [p[0] for p in pipes], mode, 9, q, one_shot))]
+    procs += [ctx.Process(target=_rank, args=(r, world, pipes[r - 1][1], mode, 9, q, one_shot)) for r in range(1, world)]
     for p in procs:
         p.start()
     out, ndev, xms = q.get(timeout=180)
