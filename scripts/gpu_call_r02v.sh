@@ -3,7 +3,7 @@
 N=${1:-2}
 mkdir -p gpurun_out
 T=r02v2
-python -m pytest tests/test_multi_gpu.py tests/test_cli.py -m gpu -q > gpurun_out/${T}_pytest_multi.log 2>&1; echo "pytest rc=$?" >> gpurun_out/${T}_pytest_multi.log
+[ "$N" = 2 ] && { python -m pytest tests/test_multi_gpu.py tests/test_cli.py -m gpu -q > gpurun_out/${T}_pytest_multi.log 2>&1; echo "pytest rc=$?" >> gpurun_out/${T}_pytest_multi.log; }
 tail -4 gpurun_out/${T}_pytest_multi.log
 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $N \
   > gpurun_out/${T}_bench_n$N.json 2> gpurun_out/${T}_bench_n$N.err; echo "n$N rc=$?"
