@@ -488,7 +488,7 @@ int main(int argc, char** argv) {
                 pool, 32 * qcost / nseg, 32 * front_cost / nseg, 32 * shade_cost / nseg, 32 * (qcost + front_cost + shade_cost) / nseg, 32 * qsteps / nseg, 100.0 * lane_active / (32.0 * qsteps));
     std::printf("QUEUE vs kernel, warp instructions per segment-lane: %.1f vs %.1f\n", (qcost + front_cost + shade_cost) / nseg, cost / lanes);
   }
-  // ---- SIM_GRID=lambda: the tree replaced by a uniform grid over its spheres (what flatten.cpp build_grid builds) ----
+  // ---- SIM_GRID=lambda: the tree replaced by a uniform grid over its spheres (what flatten.cpp choose_grids / emit_grids build) ----
   if (const char* ge = std::getenv("SIM_GRID")) {
     const double lambda = std::atof(ge);
     struct Box { float lo[3], hi[3]; int prim; };

@@ -1,13 +1,15 @@
-"""The uniform grid of sphere fields (flatten.cpp build_grid, intersect.cuh grid_hit32).
+"""The uniform grids of even fields (flatten.cpp choose_grids / emit_grids, intersect.cuh grid_hit32).
 
-An even field of spheres — the book-1 final scene (in_one_weekend/mod.rs:65-108), the bouncing spheres
-of book 2 (the_next_week/mod.rs:96-149) — is walked cell by cell instead of through the BVH.  The grid
-only changes WHERE the candidates come from: every sphere test is sphere_hit32's, so hits, equal-t
-decisions and therefore whole frames must be those of the tree walk, bit for bit.
+An even field of equal items — the small spheres of the book-1 final scene (in_one_weekend/mod.rs:65-108), the
+bouncing spheres of book 2 (the_next_week/mod.rs:96-149), the ground boxes and the sphere cloud of the book-2 final
+scene (:507-605) — is walked cell by cell instead of through the BVH, and whatever is left sits in the front run.
+The grid only changes WHERE the candidates come from: every test is sphere_hit32's / the box-leaf test's, so hits,
+equal-t decisions and therefore whole frames must be those of the tree walk — bit for bit, except for boxes that tile
+a lattice, where a ray within f32 rounding of a vertical box edge may be settled the other way round.
 
-CPU tier: which scenes get a grid, and the flattener's own check of the cell tables (every sphere
-referenced from every cell its swept box overlaps).  GPU tier: f32 probe and deterministic renders with
-and without the grid are identical; forced grids over uneven random sphere scenes as well.
+CPU tier: which scenes get grids, and the flattener's own check of the cell tables (every item referenced from every
+cell it reaches).  GPU tier: f32 probe and deterministic renders with and without the grids; forced grids over uneven
+random sphere scenes and over random box fields; the one-shot render that builds no tree.
 """
 import numpy as np
 import pytest
