@@ -1,17 +1,20 @@
 """A second witness for the scene builders of librrt_host.so (rustraytrace_b200/host/books.cpp).
 
 Every parity test hands the oracle and the GPU the same rrt_scene_desc, so an error in the C++ scene
-builders would be invisible to them.  This module restates two flagship scenes in pure Python, read
-from the reference's Rust sources and NOT from books.cpp:
-    in_one_weekend::run            src/books/in_one_weekend/mod.rs:57-126         (configs C1, C2)
-    the_next_week::final_scene     src/books/the_next_week/mod.rs:507-624         (config C4)
+builders would be invisible to them.  This module restates the scenes behind every BASELINE.json config in
+pure Python, read from the reference's Rust sources and NOT from books.cpp:
+    in_one_weekend::run              src/books/in_one_weekend/mod.rs:57-126         (configs C1, C2)
+    the_next_week::bouncing_spheres  src/books/the_next_week/mod.rs:83-152          (C3a)
+    the_next_week::earth, perlin_spheres                    :196-254                (C3b, C3c)
+    the_next_week::final_scene       src/books/the_next_week/mod.rs:507-624         (C4)
+    the_rest_of_your_life::run       src/books/the_rest_of_your_life/mod.rs:69-161  (C5, with its light list)
 with rand 0.8.5's SmallRng (Xoshiro256++ seeded through SplitMix64) and its gen_range(low..high)
 mapping for f64 restated from their published algorithms, in the reference's order of draws.
 tests/test_scene_witness.py walks the C description into the same nested form and compares.
 
 Test infrastructure only.  Nested form: ("sphere", c, dc, r, mat) ("quad", Q, u, v, mat) ("list" | "bvh", [..])
 ("translate", offset, child) ("rotate_y", degrees, child) ("medium", density, phase_mat, child);
-mat = (kind, albedo, fuzz, ri, tex); tex = ("solid", rgb) ("image",) ("noise", scale, perlin) or None.
+mat = (kind, albedo, fuzz, ri, tex); tex = ("solid", rgb) ("checker", scale, even, odd) ("image",) ("noise", scale, perlin) or None.
 """
 import math
 import struct
@@ -187,3 +190,74 @@ def book2_final(seed, image_width=800, samples_per_pixel=10000, max_depth=40):
                background=(0.0, 0.0, 0.0), vfov=40.0, lookfrom=(478.0, 278.0, -600.0), lookat=(278.0, 278.0, 0.0),
                vup=(0.0, 1.0, 0.0), defocus_angle=0.0)
     return ("list", world), cam
+
+
+def checker(scale, even, odd):
+    return ("checker", scale, ("solid", tuple(even)), ("solid", tuple(odd)))
+
+
+def book2_bouncing_spheres(seed):
+    """the_next_week/mod.rs:83-152 (scene 1; config C3a)."""
+    g = SmallRng(seed)
+    ground = (LAMBERTIAN, None, 0.0, 1.0, checker(0.32, (0.2, 0.3, 0.1), (0.9, 0.9, 0.9)))
+    world = [sphere((0.0, -1000.0, 0.0), 1000.0, ground)]
+    for a in range(-11, 11):
+        for b in range(-11, 11):
+            choose_mat = g.random_double()
+            center = (a + 0.9 * g.random_double(), 0.2, b + 0.9 * g.random_double())
+            if length((center[0] - 4.0, center[1] - 0.2, center[2] - 0.0)) > 0.9:
+                if choose_mat < 0.8:
+                    c1, c2 = g.random_vec(), g.random_vec()
+                    mat = lambertian(tuple(c1[i] * c2[i] for i in range(3)))
+                    center2 = (center[0], center[1] + g.random_double() * 0.5, center[2])
+                    world.append(sphere(center, 0.2, mat, c2=center2))
+                elif choose_mat < 0.95:
+                    albedo = g.random_vec_range(0.5, 1.0)
+                    world.append(sphere(center, 0.2, metal(albedo, g.random_double() * 0.5)))
+                else:
+                    world.append(sphere(center, 0.2, dielectric(1.5)))
+    world.append(sphere((0.0, 1.0, 0.0), 1.0, dielectric(1.5)))
+    world.append(sphere((-4.0, 1.0, 0.0), 1.0, lambertian((0.4, 0.2, 0.1))))
+    world.append(sphere((4.0, 1.0, 0.0), 1.0, metal((0.7, 0.6, 0.5), 0.0)))
+    cam = dict(aspect_ratio=16.0 / 9.0, image_width=400, samples_per_pixel=100, max_depth=50, background=(0.70, 0.80, 1.00),
+               vfov=20.0, lookfrom=(13.0, 2.0, 3.0), lookat=(0.0, 0.0, 0.0), vup=(0.0, 1.0, 0.0), defocus_angle=0.6, focus_dist=10.0)
+    return ("bvh", world), cam
+
+
+def book2_earth():
+    """the_next_week/mod.rs:196-219 (scene 3; config C3b)."""
+    world = [sphere((0.0, 0.0, 0.0), 2.0, (LAMBERTIAN, None, 0.0, 1.0, ("image",)))]
+    cam = dict(aspect_ratio=16.0 / 9.0, image_width=400, samples_per_pixel=100, max_depth=50, background=(0.70, 0.80, 1.00),
+               vfov=20.0, lookfrom=(0.0, 0.0, 12.0), lookat=(0.0, 0.0, 0.0), vup=(0.0, 1.0, 0.0), defocus_angle=0.0)
+    return ("list", world), cam
+
+
+def book2_perlin_spheres(seed):
+    """the_next_week/mod.rs:221-254 (scene 4; config C3c): one NoiseTexture shared by both spheres."""
+    g = SmallRng(seed)
+    pertext = ("noise", 4.0, perlin_new(g))
+    world = [sphere((0.0, -1000.0, 0.0), 1000.0, (LAMBERTIAN, None, 0.0, 1.0, pertext)),
+             sphere((0.0, 2.0, 0.0), 2.0, (LAMBERTIAN, None, 0.0, 1.0, pertext))]
+    cam = dict(aspect_ratio=16.0 / 9.0, image_width=400, samples_per_pixel=100, max_depth=50, background=(0.70, 0.80, 1.00),
+               vfov=20.0, lookfrom=(13.0, 2.0, 3.0), lookat=(0.0, 0.0, 0.0), vup=(0.0, 1.0, 0.0), defocus_angle=0.0)
+    return ("list", world), cam
+
+
+def book3_cornell():
+    """the_rest_of_your_life/mod.rs:69-161 (config C5).  Returns (world, lights, camera dict)."""
+    red, white, green = lambertian((0.65, 0.05, 0.05)), lambertian((0.73, 0.73, 0.73)), lambertian((0.12, 0.45, 0.15))
+    light = (DIFFUSE_LIGHT, (15.0, 15.0, 15.0), 0.0, 1.0, ("solid", (15.0, 15.0, 15.0)))
+    world = [("quad", (555.0, 0.0, 0.0), (0.0, 0.0, 555.0), (0.0, 555.0, 0.0), green),
+             ("quad", (0.0, 0.0, 555.0), (0.0, 0.0, -555.0), (0.0, 555.0, 0.0), red),
+             ("quad", (0.0, 555.0, 0.0), (555.0, 0.0, 0.0), (0.0, 0.0, 555.0), white),
+             ("quad", (0.0, 0.0, 555.0), (555.0, 0.0, 0.0), (0.0, 0.0, -555.0), white),
+             ("quad", (555.0, 0.0, 555.0), (-555.0, 0.0, 0.0), (0.0, 555.0, 0.0), white),
+             ("quad", (213.0, 554.0, 227.0), (130.0, 0.0, 0.0), (0.0, 0.0, 105.0), light),
+             ("translate", (265.0, 0.0, 295.0), ("rotate_y", 15.0, make_box((0.0, 0.0, 0.0), (165.0, 330.0, 165.0), white))),
+             sphere((190.0, 90.0, 190.0), 90.0, dielectric(1.5))]
+    empty = ("empty", None, 0.0, 1.0, None)
+    lights = ("list", [("quad", (343.0, 554.0, 332.0), (-130.0, 0.0, 0.0), (0.0, 0.0, -105.0), empty),
+                       sphere((190.0, 90.0, 190.0), 90.0, empty)])
+    cam = dict(aspect_ratio=1.0, image_width=600, samples_per_pixel=100, max_depth=50, background=(0.0, 0.0, 0.0), vfov=40.0,
+               lookfrom=(278.0, 278.0, -800.0), lookat=(278.0, 278.0, 0.0), vup=(0.0, 1.0, 0.0), defocus_angle=0.0)
+    return ("bvh", world), lights, cam

@@ -1,6 +1,7 @@
 """librrt_host.so's scene builders (host/books.cpp) against an independent restatement of the reference's Rust
 scene code (tests/scene_witness.py): same seed, same order of draws — every primitive, transform, material,
-texture and Perlin table of the book-1 final scene (C1, C2) and of the book-2 final scene (C4) must agree.
+texture, Perlin table and light of the scenes behind C1-C5 (book-1 final, bouncing spheres, earth, Perlin spheres, book-2
+final, book-3 Cornell box) must agree.
 The oracle and the GPU both consume books.cpp's output, so this is what makes a scene-builder error visible."""
 import math
 
@@ -10,7 +11,7 @@ import scene_witness as W
 F = R._ffi
 SEED = 0x5EED1234   # BookScene's default, the reference's GPU-path seed (src/gpu/mod.rs:199)
 MAT = {F.M_LAMBERTIAN: W.LAMBERTIAN, F.M_METAL: W.METAL, F.M_DIELECTRIC: W.DIELECTRIC, F.M_DIFFUSE_LIGHT: W.DIFFUSE_LIGHT,
-       F.M_ISOTROPIC: W.ISOTROPIC}
+       F.M_ISOTROPIC: W.ISOTROPIC, F.M_EMPTY: "empty"}
 
 
 def v3(d):
@@ -28,6 +29,8 @@ def walk(desc, idx):
             return ("solid", v3(x.color))
         if x.kind == F.T_IMAGE:
             return ("image",)
+        if x.kind == F.T_CHECKER:
+            return ("checker", x.scale, tex(x.even), tex(x.odd))
         if x.kind == F.T_NOISE:
             p = desc.perlins[x.perlin]
             return ("noise", x.scale, ([v3(p.randvec[i]) for i in range(256)], list(p.perm_x), list(p.perm_y), list(p.perm_z)))
@@ -122,4 +125,21 @@ def test_book2_final_scene_matches_the_rust_source():
     s = R.BookScene("the_next_week", 9, seed=SEED)
     world, cam = W.book2_final(SEED)
     same_scene(walk(s.desc, s.desc.world), world)
+    same_camera(s.camera, cam)
+
+
+def test_book2_configs_c3_match_the_rust_source():
+    """Bouncing spheres (C3a: moving spheres, checker ground), earth (C3b), Perlin spheres (C3c: one shared noise texture)."""
+    for no, (world, cam) in ((1, W.book2_bouncing_spheres(SEED)), (3, W.book2_earth()), (4, W.book2_perlin_spheres(SEED))):
+        s = R.BookScene("the_next_week", no, seed=SEED, overrides={})
+        same_scene(walk(s.desc, s.desc.world), world, f"scene{no}")
+        same_camera(s.camera, cam)
+
+
+def test_book3_cornell_box_and_its_light_list_match_the_rust_source():
+    s = R.BookScene("the_rest_of_your_life", None, seed=SEED, overrides={})
+    world, lights, cam = W.book3_cornell()
+    same_scene(walk(s.desc, s.desc.world), world)
+    assert s.desc.lights >= 0
+    same_scene(walk(s.desc, s.desc.lights), lights, "lights")
     same_camera(s.camera, cam)
