@@ -53,26 +53,25 @@ __device__ inline float perlin_noise(const DevPerlin* __restrict__ P, V3f p) {
   float uu = u * u * (3.0f - 2.0f * u);
   float vv = v * v * (3.0f - 2.0f * v);
   float ww = w * w * (3.0f - 2.0f * w);
-  float accum = 0.0f;
+  // perlin_interp (perlin.rs:78-96) is the trilinear blend of the eight corner products with weights uu, vv, ww; written
+  // as nested lerps (along z, then y, then x: 7 x 2 operations) instead of eight triple products and sums (C3c +3 %)
+  const int pz0 = perlin_perm<SHARED>(P, 2, k & 255), pz1 = perlin_perm<SHARED>(P, 2, (k + 1) & 255);
+  float along_x[2];
 #pragma unroll
   for (int di = 0; di < 2; ++di) {
-    int px = perlin_perm<SHARED>(P, 0, (i + di) & 255);
-    float wi = di ? uu : 1.0f - uu;
+    const int px = perlin_perm<SHARED>(P, 0, (i + di) & 255);
+    float along_y[2];
 #pragma unroll
     for (int dj = 0; dj < 2; ++dj) {
-      int py = perlin_perm<SHARED>(P, 1, (j + dj) & 255);
-      float wj = dj ? vv : 1.0f - vv;
-#pragma unroll
-      for (int dk = 0; dk < 2; ++dk) {
-        int pz = perlin_perm<SHARED>(P, 2, (k + dk) & 255);
-        float wk = dk ? ww : 1.0f - ww;
-        float4 g = perlin_grad<SHARED>(P, px ^ py ^ pz);
-        float dp = g.x * (u - di) + g.y * (v - dj) + g.z * (w - dk);
-        accum += wi * wj * wk * dp;
-      }
+      const int pxy = px ^ perlin_perm<SHARED>(P, 1, (j + dj) & 255);
+      const float4 g0 = perlin_grad<SHARED>(P, pxy ^ pz0), g1 = perlin_grad<SHARED>(P, pxy ^ pz1);
+      const float d0 = g0.x * (u - di) + g0.y * (v - dj) + g0.z * w;
+      const float d1 = g1.x * (u - di) + g1.y * (v - dj) + g1.z * (w - 1.0f);
+      along_y[dj] = fmaf(ww, d1 - d0, d0);
     }
+    along_x[di] = fmaf(vv, along_y[1] - along_y[0], along_y[0]);
   }
-  return accum;
+  return fmaf(uu, along_x[1] - along_x[0], along_x[0]);
 }
 
 template <bool SHARED>

@@ -1,11 +1,6 @@
 #!/bin/bash
-# Packed sphere pairs in the front run: A/B RRT_NO_FRONT_PAIRS=1, and the tests that hold front run against tree bit for bit.
+# perlin_interp as nested lerps: C3c, C4 numbers and the tests that see noise textures.
 mkdir -p gpurun_out
-T=r02y4
-python scripts/gpu_quick.py 500 C2,C3a,C4 > gpurun_out/${T}_a.log 2>&1
-RRT_NO_FRONT_PAIRS=1 python scripts/gpu_quick.py 500 C2,C3a,C4 > gpurun_out/${T}_b.log 2>&1
-python scripts/gpu_quick.py 100 C1 >> gpurun_out/${T}_a.log 2>&1
-RRT_NO_FRONT_PAIRS=1 python scripts/gpu_quick.py 100 C1 >> gpurun_out/${T}_b.log 2>&1
-cut -c1-130 gpurun_out/${T}_a.log gpurun_out/${T}_b.log
-python -m pytest tests -m gpu -q -x > gpurun_out/${T}_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/${T}_pytest.log
-tail -12 gpurun_out/${T}_pytest.log
+T=r02y6
+python scripts/gpu_quick.py 500 C3c,C4 > gpurun_out/${T}.log 2>&1; cut -c1-190 gpurun_out/${T}.log
+python -m pytest tests/test_converged_golden.py tests/test_gpu_parity.py tests/test_golden.py tests/test_full_size.py -m gpu -q -x 2>&1 | tail -3
